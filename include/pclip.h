@@ -1,0 +1,203 @@
+/*
+ * pclip.h -- C ABI of libpclip.so, the B200 (sm_100a) implementation of protein-clip's contrastive hot path.
+ *
+ * The reference (pan-emily/protein-clip) has NO native / FFI boundary: its hot path is a handful of
+ * Python functions built from torch library ops.  Each entry point below therefore cites the Python
+ * call site it replaces ("ref:" = path relative to the reference checkout).  The Python host code in
+ * protein-clip_b200/pclip binds these with ctypes (see INTEGRATION.md for the exact stubs) and keeps
+ * the reference's module-level names call-compatible.
+ *
+ * Conventions
+ *   - every function returns 0 (PCLIP_OK) or a negative pclip_status; pclip_last_error() gives the
+ *     thread-local message of the last failure.
+ *   - all `void*` / `float*` data pointers are DEVICE pointers unless the comment says HOST.
+ *   - nothing here allocates or frees caller memory; scratch comes from a caller workspace whose size
+ *     is given by the matching *_workspace_bytes() query.
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises.
+ *   - no global state; calls are re-entrant per (stream, workspace).
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *     PCLIP_ERR_CUDA.
+ */
+#ifndef PCLIP_H_
+#define PCLIP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* pclip_stream_t; /* cudaStream_t */
+
+enum pclip_status {
+  PCLIP_OK = 0,
+  PCLIP_ERR_INVALID = -1,     /* bad argument (null pointer, negative size, misaligned pointer) */
+  PCLIP_ERR_UNSUPPORTED = -2, /* shape / dtype combination with no kernel (e.g. D != 128 in bf16 mode) */
+  PCLIP_ERR_CUDA = -3,        /* a CUDA runtime / driver call failed; message has the CUDA error string */
+  PCLIP_ERR_WORKSPACE = -4    /* workspace too small or misaligned (needs 1024 B alignment) */
+};
+
+enum pclip_dtype { PCLIP_F32 = 0, PCLIP_BF16 = 1 };
+
+/* arithmetic the similarity contractions run in */
+enum pclip_compute {
+  PCLIP_COMPUTE_F32 = 0, /* FP32 FFMA on CUDA cores: matches the reference's fp32 path to ~1e-6 */
+  PCLIP_COMPUTE_BF16 = 1 /* BF16 operands, FP32 accumulate, tcgen05 tensor cores (TMA + TMEM) */
+};
+
+/* A strided 2-D row block living on the device. Lists of these express GradCache's "list of leaves"
+ * without a torch.cat (ref: GradCache cat_input_tensor, modules/training_utils.py:247-249). */
+typedef struct {
+  const void* ptr;    /* device pointer to element (0,0) */
+  int64_t rows;       /* number of rows in this chunk */
+  int64_t row_stride; /* in elements */
+  int64_t col_stride; /* in elements (1 for contiguous rows, `rows`-ish for a .t() view) */
+} pclip_chunk_t;
+
+int pclip_version(void);
+const char* pclip_last_error(void);
+/* number of kernels launched by this thread through the library since the last reset (bench bookkeeping) */
+int64_t pclip_launch_count(void);
+void pclip_launch_count_reset(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * (1) Encoder tail: L2-normalise + temperature scale.
+ *     ref: modules/models.py:50-51   out = F.normalize(e, dim=-1) * exp(tau / 2)
+ *     eps = 1e-12 -> x / max(||x||, eps).  With eps == 0 and tau == NULL this is the FILIP token
+ *     normalisation, ref: modules/models.py:238-239 (h / h.norm(dim=-1, keepdim=True), no eps).
+ * ---------------------------------------------------------------------------------------------- */
+int pclip_normalize_scale_fwd(const float* e, int64_t rows, int32_t D, const float* tau /* dev [1] or NULL */,
+                              float eps, float* out /* [rows, D] */, float* inv_norm /* [rows] saved */,
+                              pclip_stream_t stream);
+/* de = (s / n) * (g - nhat * <g, nhat>),  dtau += 0.5 * sum(g * out)   (dtau may be NULL) */
+int pclip_normalize_scale_bwd(const float* grad_out, const float* out, const float* inv_norm, int64_t rows,
+                              int32_t D, const float* tau, float* de, float* dtau /* dev [1], accumulated */,
+                              pclip_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (2) CLIP InfoNCE, symmetric cross entropy over S = X Y^T.
+ *     ref: modules/training_utils.py:74-89  (_contrastive_loss)
+ *          modules/training_utils.py:247-265 (_contrastive_loss_gc: same math on concatenated leaves)
+ *     loss = 1/(2B) * sum_i [ log R_i + log C_i - 2 S_ii ],  R_i = sum_j exp S_ij, C_j = sum_i exp S_ij
+ *     dS   = 1/(2B) * [ E/R_i + E/C_j - 2 I ],  dX = dS Y,  dY = dS^T X
+ *     exp is the reference's plain exp (no max subtraction): results are identical wherever the
+ *     reference's are finite.
+ * ---------------------------------------------------------------------------------------------- */
+size_t pclip_clip_workspace_bytes(int64_t B, int32_t D, int32_t compute);
+
+/* Single-GPU composite: pack -> row/column sum-exp -> loss (-> gradients).
+ * x / y are lists of row chunks (n == 1 for a plain tensor; y may be a transposed view through strides).
+ * dx / dy: packed [B, D] fp32 gradients for grad_output == 1 (NULL = forward only). */
+int pclip_clip_loss(const pclip_chunk_t* x_chunks /* HOST */, int32_t nx, const pclip_chunk_t* y_chunks /* HOST */,
+                    int32_t ny, int32_t in_dtype, int64_t B, int32_t D, int32_t compute,
+                    float* loss /* [1] */, float* row_lse /* [B] or NULL */, float* col_lse /* [B] or NULL */,
+                    float* dx, float* dy, void* workspace, size_t workspace_bytes, pclip_stream_t stream);
+
+/* Building blocks (used by the composite above and by the multi-GPU row-sharded path, where `a` holds the
+ * rank's own rows and `b` the all-gathered other modality). */
+
+/* pack chunk lists into contiguous [rows, D] matrices of the compute dtype (fp32 or bf16) */
+int pclip_pack(const pclip_chunk_t* chunks /* HOST */, int32_t n, int32_t in_dtype, int64_t rows, int32_t D,
+               int32_t out_dtype, void* out, pclip_stream_t stream);
+
+typedef struct {
+  const void* a;       /* [Ma, D] packed, compute dtype */
+  const void* b;       /* [Nb, D] packed, compute dtype */
+  int64_t Ma, Nb;
+  int64_t diag_offset; /* row i of `a` is the positive of row diag_offset + i of `b` */
+  float* rowsum;       /* out [Ma]: sum_j exp(a_i . b_j) */
+  float* diag;         /* out [Ma]: a_i . b_(diag_offset+i), or NULL */
+} pclip_clip_fwd_side_t;
+
+int pclip_clip_rowsumexp(const pclip_clip_fwd_side_t* sides /* HOST */, int32_t n_sides /* 1 or 2 */, int32_t D,
+                         int32_t compute, pclip_stream_t stream);
+
+/* per-row loss terms -> row_lse/col_lse, 1/R, 1/C and sum_i(log R_i + log C_i - 2 diag_i) * scale */
+int pclip_clip_finalize(const float* rowsum, const float* colsum, const float* diag, int64_t M, float scale,
+                        float* row_lse, float* col_lse, float* rinv, float* cinv, float* loss /* [1] */,
+                        pclip_stream_t stream);
+
+typedef struct {
+  const void* a;
+  const void* b;
+  int64_t Ma, Nb;
+  int64_t diag_offset;
+  const float* rinv; /* [Ma] 1 / (sum-exp of row i) */
+  const float* cinv; /* [Nb] 1 / (sum-exp of column j) */
+  float* da;         /* out [Ma, D] fp32: scale * (sum_j exp(s_ij) (rinv_i + cinv_j) b_j - 2 b_(diag_offset+i)) */
+} pclip_clip_bwd_side_t;
+
+int pclip_clip_grad(const pclip_clip_bwd_side_t* sides /* HOST */, int32_t n_sides, int32_t D, int32_t compute,
+                    float scale, pclip_stream_t stream);
+
+/* out[i] = in[i] * (*g)   -- applies autograd's scalar grad_output (GradScaler passes 65536, ref:
+ * modules/training_utils.py:139) on the device, no host sync */
+int pclip_scale_by_scalar(const float* in, const float* g /* dev [1] */, int64_t n, float* out,
+                          pclip_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (3) Similarity scores / rank-of-positive / top-k retrieval.
+ *     ref: modules/training_utils.py:157-172 (get_logits: exp(x y^T))
+ *          modules/visualizations.py:38-52   (cosine matrix: x y^T * exp(-tau))
+ *          modules/training_utils.py:219-222 (rank = #{j: s_j > s_pos} + 1, strict >)
+ *          topk.py:47-61                     (top-k accuracy = cumulative rank histogram)
+ * ---------------------------------------------------------------------------------------------- */
+enum pclip_score_op { PCLIP_SCORE_DOT = 0, PCLIP_SCORE_EXP = 1 };
+
+/* out[q, n] = op(q . bank_n) * (mul_tau ? exp(-*tau) : 1);  q, bank packed fp32 */
+int pclip_scores(const float* q, const float* bank, int64_t Q, int64_t N, int32_t D, int32_t op,
+                 const float* neg_tau /* dev [1] or NULL: multiply by exp(-tau) */, float* out, pclip_stream_t stream);
+
+/* rank[q] = 1 + #{ n : q.bank_n > q.bank_pos[q] }  in exact fp32 */
+int pclip_rank_of_positive(const float* q, const float* bank, const int64_t* pos, int64_t Q, int64_t N, int32_t D,
+                           int32_t* rank, pclip_stream_t stream);
+
+size_t pclip_topk_workspace_bytes(int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute);
+/* top-k by dot product, descending, ties -> lower index.  idx [Q,k] int64, score [Q,k] fp32 (exact fp32
+ * re-scored values).  compute == BF16: tensor-core candidate selection + exact fp32 rescoring of the
+ * candidates; `n_unsafe` (dev [1], may be NULL) counts queries whose candidate margin could not prove
+ * exactness (those rows are then recomputed in exact fp32 by the library). */
+int pclip_topk(const float* q, const float* bank, int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute,
+               int64_t index_base, int64_t* idx, float* score, int32_t* n_unsafe, void* workspace,
+               size_t workspace_bytes, pclip_stream_t stream);
+/* merge per-shard (idx, score) candidate lists [Q, n_lists*k] into the global top-k (bank-sharded mode) */
+int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, int32_t n_lists, int32_t k,
+                     int64_t* idx, float* score, pclip_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * (4) FILIP token-wise late interaction.
+ *     ref: modules/models.py:292-356 (_filip_similarity_score), :247-264 (_masked_mean)
+ *          modules/training_utils_filip.py:4-39 (_contrastive_loss row-wise on BOTH matrices, _compute_loss)
+ *     S[a,b,t,s] = <hA[a,t], hB[b,s]> / tau, pads masked to -FLT_MAX;
+ *     simA[a,b] = mean_{t valid} max_s S,  simB[a,b] = mean_{s valid} max_t S.
+ *     argA[a,b,t] / argB[a,b,s] record the maximising token (lowest index on exact ties) for backward.
+ * ---------------------------------------------------------------------------------------------- */
+size_t pclip_filip_workspace_bytes(int64_t Ba, int64_t Bb, int64_t TA, int64_t TB, int32_t D, int32_t compute);
+
+int pclip_filip_fwd(const float* hA /* [Ba,TA,D] */, const float* hB /* [Bb,TB,D] */,
+                    const uint8_t* maskA /* [Ba,TA] */, const uint8_t* maskB /* [Bb,TB] */, int64_t Ba, int64_t Bb,
+                    int64_t TA, int64_t TB, int32_t D, const float* tau /* dev [1] */, int32_t compute,
+                    float* simA /* [Ba,Bb] */, float* simB /* [Ba,Bb] */, int16_t* argA /* [Ba,Bb,TA] or NULL */,
+                    int16_t* argB /* [Ba,Bb,TB] or NULL */, void* workspace, size_t workspace_bytes,
+                    pclip_stream_t stream);
+
+/* gA / gB: upstream gradients of simA / simB [Ba,Bb].  dhA [Ba,TA,D], dhB [Bb,TB,D] are OVERWRITTEN,
+ * dtau [1] is accumulated. */
+int pclip_filip_bwd(const float* hA, const float* hB, const uint8_t* maskA, const uint8_t* maskB, int64_t Ba,
+                    int64_t Bb, int64_t TA, int64_t TB, int32_t D, const float* tau, const float* simA,
+                    const float* simB, const int16_t* argA, const int16_t* argB, const float* gA, const float* gB,
+                    float* dhA, float* dhB, float* dtau, void* workspace, size_t workspace_bytes,
+                    pclip_stream_t stream);
+
+/* row-wise InfoNCE on a [B, Bc] logits matrix whose positives sit at column diag_offset + i:
+ *   loss = scale * sum_i (log sum_j exp L_ij - L_i,diag);  dlogits = scale * (softmax_row - onehot)
+ * ref: modules/training_utils_filip.py:15-23 */
+int pclip_rowwise_infonce(const float* logits, int64_t B, int64_t Bc, int64_t diag_offset, float scale,
+                          float* loss /* [1], accumulated */, float* dlogits /* [B,Bc] or NULL */,
+                          pclip_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCLIP_H_ */

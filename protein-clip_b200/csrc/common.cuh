@@ -1,0 +1,82 @@
+// Host-side plumbing shared by every translation unit of libpclip.so.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/pclip.h"
+
+namespace pclip {
+
+// thread-local error text + launch counter (defined in api.cu)
+int fail(int code, const char* fmt, ...);
+void count_launch(int n = 1);
+
+#define PCLIP_CHECK_CUDA(expr)                                                                        \
+  do {                                                                                                \
+    cudaError_t _e = (expr);                                                                          \
+    if (_e != cudaSuccess)                                                                            \
+      return ::pclip::fail(PCLIP_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),    \
+                           __FILE__, __LINE__);                                                       \
+  } while (0)
+
+#define PCLIP_CHECK_LAUNCH()                                                                          \
+  do {                                                                                                \
+    cudaError_t _e = cudaGetLastError();                                                              \
+    if (_e != cudaSuccess)                                                                            \
+      return ::pclip::fail(PCLIP_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e),\
+                           __FILE__, __LINE__);                                                       \
+    ::pclip::count_launch();                                                                          \
+  } while (0)
+
+#define PCLIP_REQUIRE(cond, code, ...)                                                                \
+  do {                                                                                                \
+    if (!(cond)) return ::pclip::fail(code, __VA_ARGS__);                                             \
+  } while (0)
+
+#define PCLIP_TRY(expr)                                                                               \
+  do {                                                                                                \
+    int _r = (expr);                                                                                  \
+    if (_r != PCLIP_OK) return _r;                                                                    \
+  } while (0)
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// bump allocator over the caller's workspace
+struct Workspace {
+  char* base;
+  size_t size;
+  size_t off = 0;
+  Workspace(void* p, size_t n) : base(static_cast<char*>(p)), size(n) {}
+  template <class T>
+  T* take(size_t count) {
+    off = align_up(off, 1024);
+    T* r = reinterpret_cast<T*>(base + off);
+    off += count * sizeof(T);
+    return r;
+  }
+  bool ok() const { return off <= size; }
+};
+
+// 2-D bf16 row-major [rows, cols] tensor map with a [box_rows, 64] box and 128-byte swizzle (tma.cu)
+int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                      uint32_t box_cols);
+// 3-D bf16 [d0=batch, d1=tokens, d2=cols] (cols innermost), box [1, box_rows, 64]
+int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, uint64_t batch, uint64_t rows, uint64_t cols,
+                      uint32_t box_rows, uint32_t box_cols);
+
+int device_sm_count();
+
+// ---- kernel-family entry points (one per .cu) ----------------------------------------------
+// FP32 CUDA-core path
+int simt_rowsumexp(const pclip_clip_fwd_side_t* sides, int n_sides, int D, cudaStream_t st);
+int simt_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, cudaStream_t st);
+// BF16 tcgen05 path
+int tc_rowsumexp(const pclip_clip_fwd_side_t* sides, int n_sides, int D, cudaStream_t st);
+int tc_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, cudaStream_t st);
+
+}  // namespace pclip
