@@ -10,9 +10,9 @@
  * Conventions
  *   - every function returns 0 (PCLIP_OK) or a negative pclip_status; pclip_last_error() gives the
  *     thread-local message of the last failure.
- *   - all `void*` / `float*` data pointers are DEVICE pointers unless the comment says HOST.
+ *   - all data pointers are DEVICE pointers unless the comment says HOST.
  *   - nothing here allocates or frees caller memory; scratch comes from a caller workspace whose size
- *     is given by the matching *_workspace_bytes() query.
+ *     is given by the matching *_workspace_bytes() query (1024-byte aligned).
  *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises.
  *   - no global state; calls are re-entrant per (stream, workspace).
  *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
@@ -43,16 +43,17 @@ enum pclip_dtype { PCLIP_F32 = 0, PCLIP_BF16 = 1 };
 /* arithmetic the similarity contractions run in */
 enum pclip_compute {
   PCLIP_COMPUTE_F32 = 0, /* FP32 FFMA on CUDA cores: matches the reference's fp32 path to ~1e-6 */
-  PCLIP_COMPUTE_BF16 = 1 /* BF16 operands, FP32 accumulate, tcgen05 tensor cores (TMA + TMEM) */
+  PCLIP_COMPUTE_BF16 = 1 /* BF16 operands, FP32 accumulate, tcgen05 tensor cores (TMA + TMEM); D == 128 */
 };
 
 /* A strided 2-D row block living on the device. Lists of these express GradCache's "list of leaves"
- * without a torch.cat (ref: GradCache cat_input_tensor, modules/training_utils.py:247-249). */
+ * without a torch.cat (ref: GradCache cat_input_tensor, modules/training_utils.py:247-249), and a
+ * `.t()` view (ref: modules/training_utils.py:69) through its strides. */
 typedef struct {
   const void* ptr;    /* device pointer to element (0,0) */
   int64_t rows;       /* number of rows in this chunk */
   int64_t row_stride; /* in elements */
-  int64_t col_stride; /* in elements (1 for contiguous rows, `rows`-ish for a .t() view) */
+  int64_t col_stride; /* in elements */
 } pclip_chunk_t;
 
 int pclip_version(void);
@@ -83,23 +84,19 @@ int pclip_normalize_scale_bwd(const float* grad_out, const float* out, const flo
  *     dS   = 1/(2B) * [ E/R_i + E/C_j - 2 I ],  dX = dS Y,  dY = dS^T X
  *     exp is the reference's plain exp (no max subtraction): results are identical wherever the
  *     reference's are finite.
+ *
+ *     Every contraction is expressed as a "side": rows of `a` against all rows of `b`.  R comes from the
+ *     side (X, Y), C from the side (Y, X); dX from (X, Y, 1/R, 1/C), dY from (Y, X, 1/C, 1/R).  A rank of a
+ *     row-sharded job passes its own rows as `a` and the all-gathered other modality as `b`, so that no
+ *     gradient has to be exchanged.
  * ---------------------------------------------------------------------------------------------- */
-size_t pclip_clip_workspace_bytes(int64_t B, int32_t D, int32_t compute);
 
-/* Single-GPU composite: pack -> row/column sum-exp -> loss (-> gradients).
- * x / y are lists of row chunks (n == 1 for a plain tensor; y may be a transposed view through strides).
- * dx / dy: packed [B, D] fp32 gradients for grad_output == 1 (NULL = forward only). */
-int pclip_clip_loss(const pclip_chunk_t* x_chunks /* HOST */, int32_t nx, const pclip_chunk_t* y_chunks /* HOST */,
-                    int32_t ny, int32_t in_dtype, int64_t B, int32_t D, int32_t compute,
-                    float* loss /* [1] */, float* row_lse /* [B] or NULL */, float* col_lse /* [B] or NULL */,
-                    float* dx, float* dy, void* workspace, size_t workspace_bytes, pclip_stream_t stream);
-
-/* Building blocks (used by the composite above and by the multi-GPU row-sharded path, where `a` holds the
- * rank's own rows and `b` the all-gathered other modality). */
-
-/* pack chunk lists into contiguous [rows, D] matrices of the compute dtype (fp32 or bf16) */
+/* pack chunk lists into a contiguous [rows, D] matrix of `out_dtype`; optionally also the transposed copy
+ * outT [D, ldT] (ldT >= rows, multiple of 64; needed by the bf16 gradient kernel).  NULL = not wanted. */
 int pclip_pack(const pclip_chunk_t* chunks /* HOST */, int32_t n, int32_t in_dtype, int64_t rows, int32_t D,
-               int32_t out_dtype, void* out, pclip_stream_t stream);
+               int32_t out_dtype, void* out, void* outT, int64_t ldT, pclip_stream_t stream);
+/* outT[d, r] = in[r, d] for packed bf16 [rows, D] (used after an all-gather) */
+int pclip_transpose_bf16(const void* in, int64_t rows, int32_t D, void* outT, int64_t ldT, pclip_stream_t stream);
 
 typedef struct {
   const void* a;       /* [Ma, D] packed, compute dtype */
@@ -110,17 +107,20 @@ typedef struct {
   float* diag;         /* out [Ma]: a_i . b_(diag_offset+i), or NULL */
 } pclip_clip_fwd_side_t;
 
+size_t pclip_clip_rowsumexp_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, int32_t compute);
 int pclip_clip_rowsumexp(const pclip_clip_fwd_side_t* sides /* HOST */, int32_t n_sides /* 1 or 2 */, int32_t D,
-                         int32_t compute, pclip_stream_t stream);
+                         int32_t compute, void* workspace, size_t workspace_bytes, pclip_stream_t stream);
 
-/* per-row loss terms -> row_lse/col_lse, 1/R, 1/C and sum_i(log R_i + log C_i - 2 diag_i) * scale */
+/* per-row loss terms -> row_lse/col_lse, 1/R, 1/C and loss[0] (+)= scale * sum_i(log R_i + log C_i - 2 diag_i) */
 int pclip_clip_finalize(const float* rowsum, const float* colsum, const float* diag, int64_t M, float scale,
                         float* row_lse, float* col_lse, float* rinv, float* cinv, float* loss /* [1] */,
                         pclip_stream_t stream);
 
 typedef struct {
-  const void* a;
-  const void* b;
+  const void* a;     /* [Ma, D] */
+  const void* b;     /* [Nb, D] */
+  const void* bT;    /* [D, ldbT] transposed copy of b (bf16 compute only; NULL for fp32) */
+  int64_t ldbT;
   int64_t Ma, Nb;
   int64_t diag_offset;
   const float* rinv; /* [Ma] 1 / (sum-exp of row i) */
@@ -128,11 +128,23 @@ typedef struct {
   float* da;         /* out [Ma, D] fp32: scale * (sum_j exp(s_ij) (rinv_i + cinv_j) b_j - 2 b_(diag_offset+i)) */
 } pclip_clip_bwd_side_t;
 
+size_t pclip_clip_grad_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, int32_t compute);
+/* `scale` is 1/(2B) times autograd's grad_output when that is known on the host; gscale (dev [1], may be
+ * NULL) multiplies it on the device (GradScaler passes 65536, ref: modules/training_utils.py:139). */
 int pclip_clip_grad(const pclip_clip_bwd_side_t* sides /* HOST */, int32_t n_sides, int32_t D, int32_t compute,
-                    float scale, pclip_stream_t stream);
+                    float scale, const float* gscale, void* workspace, size_t workspace_bytes,
+                    pclip_stream_t stream);
 
-/* out[i] = in[i] * (*g)   -- applies autograd's scalar grad_output (GradScaler passes 65536, ref:
- * modules/training_utils.py:139) on the device, no host sync */
+/* Single-GPU composite: pack -> row/column sum-exp -> loss (-> gradients for grad_output == 1).
+ * x / y are lists of row chunks (n == 1 for a plain tensor; y may be a transposed view through strides). */
+size_t pclip_clip_workspace_bytes(int64_t B, int32_t D, int32_t compute);
+int pclip_clip_loss(const pclip_chunk_t* x_chunks /* HOST */, int32_t nx, const pclip_chunk_t* y_chunks /* HOST */,
+                    int32_t ny, int32_t in_dtype, int64_t B, int32_t D, int32_t compute,
+                    float* loss /* [1] */, float* row_lse /* [B] or NULL */, float* col_lse /* [B] or NULL */,
+                    float* dx /* [B, D] fp32 or NULL */, float* dy, void* workspace, size_t workspace_bytes,
+                    pclip_stream_t stream);
+
+/* out[i] = in[i] * (*g)   -- applies autograd's scalar grad_output on the device, no host sync */
 int pclip_scale_by_scalar(const float* in, const float* g /* dev [1] */, int64_t n, float* out,
                           pclip_stream_t stream);
 
@@ -145,23 +157,24 @@ int pclip_scale_by_scalar(const float* in, const float* g /* dev [1] */, int64_t
  * ---------------------------------------------------------------------------------------------- */
 enum pclip_score_op { PCLIP_SCORE_DOT = 0, PCLIP_SCORE_EXP = 1 };
 
-/* out[q, n] = op(q . bank_n) * (mul_tau ? exp(-*tau) : 1);  q, bank packed fp32 */
+/* out[q, n] = op(q . bank_n) * (neg_tau ? exp(-*neg_tau) : 1);  q, bank packed fp32 */
 int pclip_scores(const float* q, const float* bank, int64_t Q, int64_t N, int32_t D, int32_t op,
-                 const float* neg_tau /* dev [1] or NULL: multiply by exp(-tau) */, float* out, pclip_stream_t stream);
+                 const float* neg_tau /* dev [1] or NULL */, float* out, pclip_stream_t stream);
 
-/* rank[q] = 1 + #{ n : q.bank_n > q.bank_pos[q] }  in exact fp32 */
+/* rank[q] = 1 + #{ n : q.bank_n > q.bank_pos[q] }  in fp32 (every score computed by the same FFMA chain) */
 int pclip_rank_of_positive(const float* q, const float* bank, const int64_t* pos, int64_t Q, int64_t N, int32_t D,
                            int32_t* rank, pclip_stream_t stream);
 
 size_t pclip_topk_workspace_bytes(int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute);
-/* top-k by dot product, descending, ties -> lower index.  idx [Q,k] int64, score [Q,k] fp32 (exact fp32
- * re-scored values).  compute == BF16: tensor-core candidate selection + exact fp32 rescoring of the
- * candidates; `n_unsafe` (dev [1], may be NULL) counts queries whose candidate margin could not prove
- * exactness (those rows are then recomputed in exact fp32 by the library). */
+/* top-k by dot product, descending, ties -> lower index.  idx [Q,k] int64 (+ index_base), score [Q,k] fp32.
+ * compute == F32: exact fp32 scores (one FFMA chain per score, d ascending).
+ * compute == BF16: tensor-core candidate selection (k + margin candidates per query) followed by fp32
+ * re-scoring of the candidates with the same FFMA chain; `n_unsafe` (dev [1], may be NULL) counts queries
+ * whose candidate margin could not prove exactness -- those rows are recomputed by the fp32 kernel. */
 int pclip_topk(const float* q, const float* bank, int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute,
                int64_t index_base, int64_t* idx, float* score, int32_t* n_unsafe, void* workspace,
                size_t workspace_bytes, pclip_stream_t stream);
-/* merge per-shard (idx, score) candidate lists [Q, n_lists*k] into the global top-k (bank-sharded mode) */
+/* merge per-shard (idx, score) candidate lists [n_lists, Q, k] into the global top-k (bank-sharded mode) */
 int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, int32_t n_lists, int32_t k,
                      int64_t* idx, float* score, pclip_stream_t stream);
 
@@ -169,14 +182,14 @@ int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, in
  * (4) FILIP token-wise late interaction.
  *     ref: modules/models.py:292-356 (_filip_similarity_score), :247-264 (_masked_mean)
  *          modules/training_utils_filip.py:4-39 (_contrastive_loss row-wise on BOTH matrices, _compute_loss)
- *     S[a,b,t,s] = <hA[a,t], hB[b,s]> / tau, pads masked to -FLT_MAX;
- *     simA[a,b] = mean_{t valid} max_s S,  simB[a,b] = mean_{s valid} max_t S.
+ *     S[a,b,t,s] = <hA[a,t], hB[b,s]> / tau over the valid prefixes lenA[a] x lenB[b];
+ *     simA[a,b] = mean_{t valid} max_s S,  simB[a,b] = mean_{s valid} max_t S  (0 when a side is empty).
  *     argA[a,b,t] / argB[a,b,s] record the maximising token (lowest index on exact ties) for backward.
  * ---------------------------------------------------------------------------------------------- */
 size_t pclip_filip_workspace_bytes(int64_t Ba, int64_t Bb, int64_t TA, int64_t TB, int32_t D, int32_t compute);
 
 int pclip_filip_fwd(const float* hA /* [Ba,TA,D] */, const float* hB /* [Bb,TB,D] */,
-                    const uint8_t* maskA /* [Ba,TA] */, const uint8_t* maskB /* [Bb,TB] */, int64_t Ba, int64_t Bb,
+                    const int32_t* lenA /* [Ba] */, const int32_t* lenB /* [Bb] */, int64_t Ba, int64_t Bb,
                     int64_t TA, int64_t TB, int32_t D, const float* tau /* dev [1] */, int32_t compute,
                     float* simA /* [Ba,Bb] */, float* simB /* [Ba,Bb] */, int16_t* argA /* [Ba,Bb,TA] or NULL */,
                     int16_t* argB /* [Ba,Bb,TB] or NULL */, void* workspace, size_t workspace_bytes,
@@ -184,14 +197,14 @@ int pclip_filip_fwd(const float* hA /* [Ba,TA,D] */, const float* hB /* [Bb,TB,D
 
 /* gA / gB: upstream gradients of simA / simB [Ba,Bb].  dhA [Ba,TA,D], dhB [Bb,TB,D] are OVERWRITTEN,
  * dtau [1] is accumulated. */
-int pclip_filip_bwd(const float* hA, const float* hB, const uint8_t* maskA, const uint8_t* maskB, int64_t Ba,
+int pclip_filip_bwd(const float* hA, const float* hB, const int32_t* lenA, const int32_t* lenB, int64_t Ba,
                     int64_t Bb, int64_t TA, int64_t TB, int32_t D, const float* tau, const float* simA,
                     const float* simB, const int16_t* argA, const int16_t* argB, const float* gA, const float* gB,
                     float* dhA, float* dhB, float* dtau, void* workspace, size_t workspace_bytes,
                     pclip_stream_t stream);
 
 /* row-wise InfoNCE on a [B, Bc] logits matrix whose positives sit at column diag_offset + i:
- *   loss = scale * sum_i (log sum_j exp L_ij - L_i,diag);  dlogits = scale * (softmax_row - onehot)
+ *   loss (+)= scale * sum_i (log sum_j exp L_ij - L_i,diag);  dlogits = scale * (softmax_row - onehot)
  * ref: modules/training_utils_filip.py:15-23 */
 int pclip_rowwise_infonce(const float* logits, int64_t B, int64_t Bc, int64_t diag_offset, float scale,
                           float* loss /* [1], accumulated */, float* dlogits /* [B,Bc] or NULL */,

@@ -7,6 +7,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <algorithm>
+
 #include "../../include/pclip.h"
 
 namespace pclip {
@@ -63,20 +65,31 @@ struct Workspace {
 };
 
 // 2-D bf16 row-major [rows, cols] tensor map with a [box_rows, 64] box and 128-byte swizzle (tma.cu)
-int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows,
-                      uint32_t box_cols);
+int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                      uint32_t box_rows, uint32_t box_cols);
 // 3-D bf16 [d0=batch, d1=tokens, d2=cols] (cols innermost), box [1, box_rows, 64]
 int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, uint64_t batch, uint64_t rows, uint64_t cols,
                       uint32_t box_rows, uint32_t box_cols);
 
 int device_sm_count();
+// PCLIP_OK, or PCLIP_ERR_CUDA when no device is visible (there is no CPU fallback)
+int require_device();
+
+// elementwise.cu: packs one or two operand chunk lists (same shape) with one launch
+int pack_operands(const pclip_chunk_t* x, int nx, const pclip_chunk_t* y, int ny, int in_dtype, int64_t rows, int D,
+                  int out_dtype, void* outx, void* outxT, void* outy, void* outyT, int64_t ldT, cudaStream_t st);
 
 // ---- kernel-family entry points (one per .cu) ----------------------------------------------
-// FP32 CUDA-core path
+// FP32 CUDA-core path (clip_simt.cu)
 int simt_rowsumexp(const pclip_clip_fwd_side_t* sides, int n_sides, int D, cudaStream_t st);
-int simt_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, cudaStream_t st);
-// BF16 tcgen05 path
-int tc_rowsumexp(const pclip_clip_fwd_side_t* sides, int n_sides, int D, cudaStream_t st);
-int tc_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, cudaStream_t st);
+int simt_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, const float* gscale,
+              cudaStream_t st);
+// BF16 tcgen05 path (clip_tc.cu)
+size_t tc_rowsumexp_workspace(int64_t Ma, int64_t Nb);
+int tc_rowsumexp(const pclip_clip_fwd_side_t* sides, int n_sides, int D, void* ws, size_t ws_bytes,
+                 cudaStream_t st);
+size_t tc_grad_workspace(int64_t Ma, int64_t Nb);
+int tc_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, const float* gscale, void* ws,
+            size_t ws_bytes, cudaStream_t st);
 
 }  // namespace pclip

@@ -1,0 +1,353 @@
+// HBM-bound passes around the contractions: chunk packing, L2-normalise (+ temperature), loss finalisation,
+// scalar grad_output scaling and the row-wise InfoNCE tail of FILIP.  One warp per row, float4 accesses.
+#include <cuda_bf16.h>
+#include <float.h>
+
+#include "common.cuh"
+
+namespace pclip {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// pack: list of strided row chunks -> contiguous [rows, D] (fp32 or bf16), optionally also the transposed
+// copy outT [D, ldT].  One launch packs up to two operands (blockIdx.y), so the CLIP composite packs x and y
+// (GradCache's two lists of leaves, ref: modules/training_utils.py:247-249) with a single kernel.
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxChunks = 32;
+struct PackOperand {
+  const void* ptr[kMaxChunks];
+  int64_t row_begin[kMaxChunks + 1];
+  int64_t row_stride[kMaxChunks];
+  int64_t col_stride[kMaxChunks];
+  void* out;
+  void* outT;
+  int64_t ldT;
+  int n;
+};
+struct PackArgs {
+  PackOperand op[2];
+};
+
+template <typename T>
+__device__ __forceinline__ T from_float(float v);
+template <>
+__device__ __forceinline__ float from_float<float>(float v) {
+  return v;
+}
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_float<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+
+// CTA = 32 rows x 128 columns; 256 threads (8 warps x 4 rows each, lane = column group)
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256) pack_kernel(const __grid_constant__ PackArgs args, int64_t rows, int D) {
+  const PackOperand& a = args.op[blockIdx.y];
+  __shared__ float tile[32][129];
+  const int64_t r0 = (int64_t)blockIdx.x * 32;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  TOut* out = static_cast<TOut*>(a.out);
+  TOut* outT = static_cast<TOut*>(a.outT);
+  for (int c0 = 0; c0 < D; c0 += 128) {
+#pragma unroll
+    for (int rr = 0; rr < 4; ++rr) {
+      const int lr = w * 4 + rr;
+      const int64_t r = r0 + lr;
+      if (r < rows) {
+        int k = 0;
+        while (k + 1 < a.n && r >= a.row_begin[k + 1]) ++k;
+        const TIn* src = static_cast<const TIn*>(a.ptr[k]) + (r - a.row_begin[k]) * a.row_stride[k];
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          const int c = c0 + cc * 32 + lane;
+          if (c < D) {
+            const float v = (float)src[(int64_t)c * a.col_stride[k]];
+            out[r * D + c] = from_float<TOut>(v);
+            tile[lr][cc * 32 + lane] = v;
+          }
+        }
+      }
+    }
+    if (outT) {
+      __syncthreads();
+      // 128 columns x 32 rows: warp w writes columns w, w+8, ...; lane = row
+#pragma unroll 4
+      for (int cc = w; cc < 128; cc += 8) {
+        const int c = c0 + cc;
+        const int64_t r = r0 + lane;
+        if (c < D && r < rows) outT[(int64_t)c * a.ldT + r] = from_float<TOut>(tile[lane][cc]);
+      }
+      __syncthreads();
+    }
+  }
+}
+
+template <typename TIn, typename TOut>
+static int launch_pack(const PackArgs& a, int n_ops, int64_t rows, int D, cudaStream_t st) {
+  dim3 grid((unsigned)ceil_div(rows, 32), (unsigned)n_ops);
+  pack_kernel<TIn, TOut><<<grid, 256, 0, st>>>(a, rows, D);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+static int fill_operand(PackOperand& o, const pclip_chunk_t* chunks, int n, int64_t rows, void* out, void* outT,
+                        int64_t ldT) {
+  PCLIP_REQUIRE(chunks && out && n > 0, PCLIP_ERR_INVALID, "pack: null argument");
+  PCLIP_REQUIRE(n <= kMaxChunks, PCLIP_ERR_UNSUPPORTED, "pack: at most %d chunks (got %d)", kMaxChunks, n);
+  PCLIP_REQUIRE(!outT || ldT >= rows, PCLIP_ERR_INVALID, "pack: ldT < rows");
+  o.n = n;
+  o.out = out;
+  o.outT = outT;
+  o.ldT = ldT;
+  int64_t r = 0;
+  for (int i = 0; i < n; ++i) {
+    PCLIP_REQUIRE(chunks[i].ptr && chunks[i].rows >= 0, PCLIP_ERR_INVALID, "pack: bad chunk %d", i);
+    o.ptr[i] = chunks[i].ptr;
+    o.row_begin[i] = r;
+    o.row_stride[i] = chunks[i].row_stride;
+    o.col_stride[i] = chunks[i].col_stride;
+    r += chunks[i].rows;
+  }
+  o.row_begin[n] = r;
+  PCLIP_REQUIRE(r == rows, PCLIP_ERR_INVALID, "pack: chunk rows sum to %lld, expected %lld", (long long)r,
+                (long long)rows);
+  return PCLIP_OK;
+}
+
+// packs one or two operands of identical shape with a single launch
+int pack_operands(const pclip_chunk_t* x, int nx, const pclip_chunk_t* y, int ny, int in_dtype, int64_t rows, int D,
+                  int out_dtype, void* outx, void* outxT, void* outy, void* outyT, int64_t ldT, cudaStream_t st) {
+  PackArgs a;
+  PCLIP_TRY(fill_operand(a.op[0], x, nx, rows, outx, outxT, ldT));
+  int n_ops = 1;
+  if (y) {
+    PCLIP_TRY(fill_operand(a.op[1], y, ny, rows, outy, outyT, ldT));
+    n_ops = 2;
+  }
+  if (in_dtype == PCLIP_F32 && out_dtype == PCLIP_F32) return launch_pack<float, float>(a, n_ops, rows, D, st);
+  if (in_dtype == PCLIP_F32 && out_dtype == PCLIP_BF16) return launch_pack<float, __nv_bfloat16>(a, n_ops, rows, D, st);
+  if (in_dtype == PCLIP_BF16 && out_dtype == PCLIP_F32) return launch_pack<__nv_bfloat16, float>(a, n_ops, rows, D, st);
+  if (in_dtype == PCLIP_BF16 && out_dtype == PCLIP_BF16)
+    return launch_pack<__nv_bfloat16, __nv_bfloat16>(a, n_ops, rows, D, st);
+  return fail(PCLIP_ERR_UNSUPPORTED, "pack: dtype %d -> %d", in_dtype, out_dtype);
+}
+
+// ---------------------------------------------------------------------------------------------
+// normalise (+ exp(tau/2)) forward / backward.  ref: modules/models.py:50-51 and :238-239
+// ---------------------------------------------------------------------------------------------
+__global__ void normalize_fwd_kernel(const float* __restrict__ e, int64_t rows, int D, const float* __restrict__ tau,
+                                     float eps, float* __restrict__ out, float* __restrict__ inv_norm) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (row >= rows) return;
+  const float* src = e + row * D;
+  float ss = 0.f;
+  for (int c = lane; c < D; c += 32) ss = fmaf(src[c], src[c], ss);
+  ss = warp_sum(ss);
+  const float nrm = sqrtf(ss);
+  const float inv = 1.0f / fmaxf(nrm, eps);  // eps == 0: plain division (inf/nan on a zero row, as the reference)
+  const float s = tau ? expf(0.5f * tau[0]) : 1.0f;
+  for (int c = lane; c < D; c += 32) out[row * D + c] = src[c] * inv * s;
+  if (lane == 0 && inv_norm) inv_norm[row] = (nrm > eps || eps == 0.f) ? inv : -inv;  // sign flags the clamped case
+}
+
+// de = (s * inv) * (g - nhat <g, nhat>)  (projection dropped when the norm was clamped to eps);
+// dtau += 0.5 * sum(g * out)
+__global__ void normalize_bwd_kernel(const float* __restrict__ g, const float* __restrict__ out,
+                                     const float* __restrict__ inv_norm, int64_t rows, int D,
+                                     const float* __restrict__ tau, float* __restrict__ de, float* __restrict__ dtau) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  float go = 0.f;
+  if (row < rows) {
+    const float s = tau ? expf(0.5f * tau[0]) : 1.0f;
+    const float invs = 1.0f / s;
+    const float invn = inv_norm[row];
+    const bool clamped = invn < 0.f;
+    const float inv = fabsf(invn);
+    for (int c = lane; c < D; c += 32) go = fmaf(g[row * D + c], out[row * D + c], go);
+    go = warp_sum(go);  // <g, out> = s <g, nhat>
+    const float proj = clamped ? 0.f : go * invs;
+    for (int c = lane; c < D; c += 32) {
+      const float nhat = out[row * D + c] * invs;
+      de[row * D + c] = s * inv * (g[row * D + c] - nhat * proj);
+    }
+  }
+  if (dtau) {
+    __shared__ float red[32];
+    const int w = threadIdx.x >> 5;
+    if (lane == 0) red[w] = row < rows ? go : 0.f;
+    __syncthreads();
+    if (w == 0) {
+      float v = lane < (int)(blockDim.x >> 5) ? red[lane] : 0.f;
+      v = warp_sum(v);
+      if (lane == 0) atomicAdd(dtau, 0.5f * v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// CLIP finalise.  ref: modules/training_utils.py:87-89
+// ---------------------------------------------------------------------------------------------
+__global__ void clip_finalize_kernel(const float* __restrict__ rowsum, const float* __restrict__ colsum,
+                                     const float* __restrict__ diag, int64_t M, float scale,
+                                     float* __restrict__ row_lse, float* __restrict__ col_lse,
+                                     float* __restrict__ rinv, float* __restrict__ cinv, float* __restrict__ loss) {
+  // single block: deterministic tree reduction
+  __shared__ float red[32];
+  float acc = 0.f;
+  for (int64_t i = threadIdx.x; i < M; i += blockDim.x) {
+    const float r = rowsum[i], c = colsum[i];
+    const float lr = logf(r), lc = logf(c);
+    if (row_lse) row_lse[i] = lr;
+    if (col_lse) col_lse[i] = lc;
+    if (rinv) rinv[i] = 1.0f / r;
+    if (cinv) cinv[i] = 1.0f / c;
+    acc += (lr - diag[i]) + (lc - diag[i]);
+  }
+  acc = warp_sum(acc);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) red[w] = acc;
+  __syncthreads();
+  if (w == 0) {
+    float v = lane < (int)(blockDim.x >> 5) ? red[lane] : 0.f;
+    v = warp_sum(v);
+    if (lane == 0) loss[0] = v * scale;
+  }
+}
+
+__global__ void scale_by_scalar_kernel(const float* __restrict__ in, const float* __restrict__ g, int64_t n,
+                                       float* __restrict__ out) {
+  const float s = g[0];
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = in[i] * s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// row-wise InfoNCE on [B, Bc] logits.  ref: modules/training_utils_filip.py:15-23
+// (max-subtracted LSE: equal to the reference's naive exp wherever that is finite)
+// ---------------------------------------------------------------------------------------------
+__global__ void rowwise_infonce_kernel(const float* __restrict__ logits, int64_t B, int64_t Bc, int64_t diag_offset,
+                                       float scale, float* __restrict__ loss, float* __restrict__ dlogits) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  float term = 0.f;
+  if (row < B) {
+    const float* L = logits + row * Bc;
+    float m = -FLT_MAX;
+    for (int64_t c = lane; c < Bc; c += 32) m = fmaxf(m, L[c]);
+    m = warp_max(m);
+    float s = 0.f;
+    for (int64_t c = lane; c < Bc; c += 32) s += expf(L[c] - m);
+    s = warp_sum(s);
+    const float lse = m + logf(s);
+    const int64_t dcol = diag_offset + row;
+    term = lse - L[dcol];
+    if (dlogits) {
+      const float inv = 1.0f / s;
+      for (int64_t c = lane; c < Bc; c += 32)
+        dlogits[row * Bc + c] = scale * (expf(L[c] - m) * inv - (c == dcol ? 1.f : 0.f));
+    }
+  }
+  __shared__ float red[32];
+  const int w = threadIdx.x >> 5;
+  if (lane == 0) red[w] = row < B ? term : 0.f;
+  __syncthreads();
+  if (w == 0) {
+    float v = lane < (int)(blockDim.x >> 5) ? red[lane] : 0.f;
+    v = warp_sum(v);
+    if (lane == 0) atomicAdd(loss, v * scale);
+  }
+}
+
+}  // namespace pclip
+
+using namespace pclip;
+
+extern "C" {
+
+int pclip_pack(const pclip_chunk_t* chunks, int32_t n, int32_t in_dtype, int64_t rows, int32_t D, int32_t out_dtype,
+               void* out, void* outT, int64_t ldT, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(rows > 0 && D > 0, PCLIP_ERR_INVALID, "pack: rows and D must be positive");
+  return pack_operands(chunks, n, nullptr, 0, in_dtype, rows, D, out_dtype, out, outT, nullptr, nullptr, ldT,
+                       static_cast<cudaStream_t>(stream));
+}
+
+int pclip_transpose_bf16(const void* in, int64_t rows, int32_t D, void* outT, int64_t ldT, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(in && outT && rows > 0 && D > 0 && ldT >= rows, PCLIP_ERR_INVALID, "transpose: bad argument");
+  pclip_chunk_t c = {in, rows, D, 1};
+  // a pack whose packed output goes back onto the input (same values) and whose transposed copy is outT
+  return pack_operands(&c, 1, nullptr, 0, PCLIP_BF16, rows, D, PCLIP_BF16, const_cast<void*>(in), outT, nullptr,
+                       nullptr, ldT, static_cast<cudaStream_t>(stream));
+}
+
+int pclip_normalize_scale_fwd(const float* e, int64_t rows, int32_t D, const float* tau, float eps, float* out,
+                              float* inv_norm, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(e && out && rows >= 0 && D > 0, PCLIP_ERR_INVALID, "normalize_fwd: bad argument");
+  if (rows == 0) return PCLIP_OK;
+  const int threads = 256;
+  normalize_fwd_kernel<<<(unsigned)ceil_div(rows * 32, threads), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      e, rows, D, tau, eps, out, inv_norm);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+int pclip_normalize_scale_bwd(const float* grad_out, const float* out, const float* inv_norm, int64_t rows, int32_t D,
+                              const float* tau, float* de, float* dtau, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(grad_out && out && inv_norm && de && rows >= 0 && D > 0, PCLIP_ERR_INVALID,
+                "normalize_bwd: bad argument");
+  if (rows == 0) return PCLIP_OK;
+  const int threads = 256;
+  normalize_bwd_kernel<<<(unsigned)ceil_div(rows * 32, threads), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      grad_out, out, inv_norm, rows, D, tau, de, dtau);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+int pclip_clip_finalize(const float* rowsum, const float* colsum, const float* diag, int64_t M, float scale,
+                        float* row_lse, float* col_lse, float* rinv, float* cinv, float* loss, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(rowsum && colsum && diag && loss && M > 0, PCLIP_ERR_INVALID, "finalize: bad argument");
+  clip_finalize_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(rowsum, colsum, diag, M, scale, row_lse,
+                                                                         col_lse, rinv, cinv, loss);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+int pclip_scale_by_scalar(const float* in, const float* g, int64_t n, float* out, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(in && g && out && n >= 0, PCLIP_ERR_INVALID, "scale_by_scalar: bad argument");
+  if (n == 0) return PCLIP_OK;
+  const int blocks = (int)std::min<int64_t>(ceil_div(n, 256), 148 * 16);
+  scale_by_scalar_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(in, g, n, out);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+int pclip_rowwise_infonce(const float* logits, int64_t B, int64_t Bc, int64_t diag_offset, float scale, float* loss,
+                          float* dlogits, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(logits && loss && B > 0 && Bc > 0 && diag_offset >= 0 && diag_offset + B <= Bc, PCLIP_ERR_INVALID,
+                "rowwise_infonce: bad argument");
+  const int threads = 256;
+  rowwise_infonce_kernel<<<(unsigned)ceil_div(B * 32, threads), threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      logits, B, Bc, diag_offset, scale, loss, dlogits);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+}  // extern "C"

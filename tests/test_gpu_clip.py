@@ -1,0 +1,178 @@
+"""GPU parity of the CLIP InfoNCE path (libpclip.so through the C ABI) against the oracle and the golden vectors
+generated from the reference's own functions.  Tolerances are north_star's: 1e-5 relative in fp32, 1e-2 in bf16."""
+import math
+
+import pytest
+import torch
+
+from oracle import restate as R
+
+pytestmark = pytest.mark.gpu
+
+F64 = torch.float64
+TOL = {"f32": 1e-5, "bf16": 1e-2}
+
+
+def rel_err(a, b):
+    a = torch.as_tensor(a).detach().double().cpu()
+    b = torch.as_tensor(b).detach().double().cpu()
+    assert a.shape == b.shape, (a.shape, b.shape)
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def assert_close(a, b, tol, what, atol=0.0):
+    e = rel_err(a, b)
+    if atol:
+        d = float((torch.as_tensor(a).detach().double().cpu() - torch.as_tensor(b).detach().double().cpu()).abs().max())
+        if d <= atol:
+            return
+    assert e <= tol, f"{what}: max rel err {e:.3e} > {tol:.1e}"
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from pclip import ops as o
+    return o
+
+
+def _mode(ops, name):
+    return ops.F32 if name == "f32" else ops.BF16
+
+
+def test_library_loads_and_counts_launches(ops):
+    from pclip import _lib
+    assert _lib.lib().pclip_version() >= 100
+    ops.reset_launch_count()
+    x = torch.randn(16, 128, device="cuda")
+    ops.clip_loss(x, x)
+    assert ops.launch_count() >= 3
+
+
+def test_encoder_tail(ops, golden):
+    g = golden("encoder_tail")
+    e = g["e"].cuda().requires_grad_()
+    tau = g["tau"].cuda().requires_grad_()
+    out = ops.normalize_scale(e, tau)
+    assert_close(out, g["out"], 1e-6, "normalize_scale")
+    out.backward(g["g"].cuda())
+    assert_close(e.grad, g["de"], 1e-5, "de")
+    assert_close(tau.grad, g["dtau"], 1e-5, "dtau")
+
+
+@pytest.mark.parametrize("name", ["clip_b16", "clip_b37", "clip_b256"])
+@pytest.mark.parametrize("mode", ["f32", "bf16"])
+def test_clip_golden(ops, golden, name, mode):
+    """Encoder tail + _contrastive_loss(pep, rec.t()) forward and backward (ref: training_utils.py:68-71)."""
+    g = golden(name)
+    e_pep = g["e_pep"].cuda().requires_grad_()
+    e_rec = g["e_rec"].cuda().requires_grad_()
+    tau = g["tau"].cuda().requires_grad_()
+    pep = ops.normalize_scale(e_pep, tau)
+    rec = ops.normalize_scale(e_rec, tau)
+    loss = ops.clip_loss(pep, rec.t().t(), compute=_mode(ops, mode))
+    tol = TOL[mode]
+    assert_close(loss, g["loss"], tol, "loss")
+    loss.backward()
+    assert_close(e_pep.grad, g["de_pep"], tol * 3, "de_pep")
+    assert_close(e_rec.grad, g["de_rec"], tol * 3, "de_rec")
+    assert_close(tau.grad, g["dtau"], tol * 3, "dtau")
+
+
+@pytest.mark.parametrize("mode", ["f32", "bf16"])
+def test_clip_transposed_view_and_trained_like(ops, golden, mode):
+    g = golden("clip_trained_like")
+    pep = g["pep"].cuda().requires_grad_()
+    rec = g["rec"].cuda().requires_grad_()
+    recT = rec.t()  # the reference passes rec.t() (stride (1, D)); we undo the view without copying
+    loss = ops.clip_loss(pep, recT.t(), compute=_mode(ops, mode))
+    loss.backward()
+    tol = TOL[mode]
+    assert_close(loss, g["loss"], tol, "loss")
+    assert_close(pep.grad, g["dpep"], tol * 3, "dpep")
+    assert_close(rec.grad, g["drec"], tol * 3, "drec")
+    # a genuinely strided operand: columns-major storage
+    rec_cm = g["rec"].cuda().t().contiguous().t().requires_grad_()
+    assert rec_cm.stride() == (1, rec_cm.shape[0])
+    loss2 = ops.clip_loss(g["pep"].cuda(), rec_cm, compute=_mode(ops, mode))
+    assert_close(loss2, g["loss"], tol, "loss (column-major y)")
+
+
+@pytest.mark.parametrize("mode", ["f32", "bf16"])
+def test_gradcache_leaves(ops, golden, mode):
+    """16 + 16 detached leaves of [16,128], grad_output = 65536 (ref: training_utils.py:137-139, :247-265)."""
+    g = golden("clip_gradcache_16x16")
+    xs = [t.cuda().requires_grad_() for t in g["x"]]
+    ys = [t.cuda().requires_grad_() for t in g["y"]]
+    loss = ops.clip_loss(xs, ys, compute=_mode(ops, mode))
+    tol = TOL[mode]
+    assert_close(loss, g["loss"], tol, "loss")
+    (loss * float(g["grad_output"])).backward()
+    dx = torch.stack([t.grad for t in xs])
+    dy = torch.stack([t.grad for t in ys])
+    assert_close(dx, g["dx"], tol * 3, "dx")
+    assert_close(dy, g["dy"], tol * 3, "dy")
+
+
+@pytest.mark.parametrize("B", [1, 5, 129, 200, 1000])
+def test_clip_bf16_ragged_sizes_vs_oracle_on_rounded_inputs(ops, B):
+    """The tensor-core path against the float64 oracle evaluated on the SAME bf16-rounded operands: isolates kernel
+    arithmetic (fp32 accumulate, ex2.approx, bf16 re-quantised P) from input rounding."""
+    from pclip import synth
+    x, y = synth.clip_scaled_embeddings(B, 128, cfg_id=100 + B)
+    xr, yr = R.bf16_round(x), R.bf16_round(y)
+    loss_o, dx_o, dy_o, rl_o, cl_o = R.clip_loss_and_grads(xr.double(), yr.double())
+    loss, dx, dy, rl, cl = ops.clip_loss_raw([x.cuda()], [y.cuda()], ops.BF16, True, want_lse=True)
+    assert_close(loss[0], loss_o, 1e-5, "loss", atol=1e-6)  # B = 1: the loss is exactly 0
+    assert_close(rl, rl_o, 1e-5, "row_lse")
+    assert_close(cl, cl_o, 1e-5, "col_lse")
+    assert_close(dx, dx_o, 4e-3, "dx")
+    assert_close(dy, dy_o, 4e-3, "dy")
+
+
+@pytest.mark.parametrize("mode,B", [("f32", 700), ("bf16", 4096), ("bf16", 8192 + 64)])
+def test_clip_multi_tile_vs_oracle(ops, mode, B):
+    from pclip import synth
+    x, y = synth.clip_scaled_embeddings(B, 128, cfg_id=7, trained_like=True)
+    loss_o, dx_o, dy_o, _, _ = R.clip_loss_and_grads(x.double(), y.double(), chunk=2048)
+    loss, dx, dy, _, _ = ops.clip_loss_raw([x.cuda()], [y.cuda()], _mode(ops, mode), True)
+    tol = TOL[mode]
+    assert_close(loss[0], loss_o, tol, "loss")
+    assert_close(dx, dx_o, tol * 3, "dx")
+    assert_close(dy, dy_o, tol * 3, "dy")
+
+
+def test_clip_full_size_properties(ops):
+    """cfg 4 (B = 65 536, bf16): size-independent properties instead of an O(B^2) oracle pass.
+    (a) all-zero embeddings: every logit is 0, so loss = ln B and both gradients vanish;
+    (b) row / column LSEs and gradient rows of a 256-row sample against the float64 oracle restricted to those
+        rows, and the loss against its definition from the kernel's own LSEs."""
+    B, D = 65536, 128
+    z = torch.zeros(B, D, device="cuda")
+    loss, dx, dy, _, _ = ops.clip_loss_raw([z], [z], ops.BF16, True)
+    assert abs(float(loss[0]) - math.log(B)) < 1e-4
+    assert float(dx.abs().max()) == 0.0 and float(dy.abs().max()) == 0.0
+    from pclip import synth
+    x, y = synth.clip_scaled_embeddings(B, D, cfg_id=4)
+    loss, dx, dy, rl, cl = ops.clip_loss_raw([x.cuda()], [y.cuda()], ops.BF16, True, want_lse=True)
+    # oracle on a row sample: row LSE of 256 rows of x against all y, column LSE of 256 rows of y against all x
+    idx = torch.arange(0, B, B // 256)
+    xr, yr = R.bf16_round(x).double(), R.bf16_round(y).double()
+    rl_o = torch.logsumexp(xr[idx] @ yr.t(), dim=1)
+    cl_o = torch.logsumexp(yr[idx] @ xr.t(), dim=1)
+    assert_close(rl.cpu()[idx], rl_o, 1e-5, "row_lse sample")
+    assert_close(cl.cpu()[idx], cl_o, 1e-5, "col_lse sample")
+    diag = (xr * yr).sum(-1)
+    # loss from its definition with the kernel's own LSEs and the exact diagonal
+    loss_def = (rl.double().cpu() + cl.double().cpu() - 2 * diag).sum() / (2 * B)
+    assert_close(loss[0], loss_def, 1e-5, "loss vs definition")
+    # gradient rows of the sample against the closed form with the kernel's LSEs
+    e = (xr[idx] @ yr.t())
+    g = (torch.exp(e - rl.double().cpu()[idx, None]) + torch.exp(e - cl.double().cpu()[None, :]))
+    dx_o = (g @ yr - 2 * yr[idx]) / (2 * B)
+    assert_close(dx.cpu()[idx], dx_o, 4e-3, "dx sample")
+
+
+def test_no_cpu_fallback(ops):
+    from pclip import _lib
+    with pytest.raises(_lib.PclipError):
+        ops.clip_loss(torch.randn(4, 128), torch.randn(4, 128))
