@@ -250,3 +250,29 @@ def bf16_round(t: torch.Tensor) -> torch.Tensor:
 
 def ln(x: float) -> float:
     return math.log(x)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# bounded CPU-baseline samples (bench.py's cpu_baseline / --impl reference legs time these)
+# ---------------------------------------------------------------------------------------------------------
+def clip_rowblock_fwd_bwd(x: torch.Tensor, y: torch.Tensor, i0: int, n: int):
+    """The work the reference arithmetic (modules/training_utils.py:85-89 + its autograd backward) spends on rows
+    [i0, i0+n) of a B-pair batch: the [n, B] block of S and E (forward), and that block's share of dX and dY
+    (backward: G block, G y, G^T x).  Column sums of a row block are partial, so the numbers are only a TIMING
+    unit (n / B of one full fwd+bwd), not a loss value; the full-size value comes from clip_loss_and_grads."""
+    xs = x[i0:i0 + n]
+    s = xs @ y.t()                       # :85
+    e = s.exp()                          # :86
+    r = e.sum(1)                         # :87
+    c = e.sum(0)                         # :88 (partial)
+    g = e * (1 / r[:, None] + 1 / c[None, :])
+    idx = torch.arange(i0, i0 + n)
+    g[idx - i0, idx] -= 2
+    dx = g @ y
+    dy = g.t() @ xs
+    return r, c, dx, dy
+
+
+def topk_block(q: torch.Tensor, bank: torch.Tensor, k: int):
+    """torch.topk over one query block (the CPU-baseline unit SURVEY.md 8(d) names for cfg 5)."""
+    return torch.topk(q @ bank.t(), k, dim=1)

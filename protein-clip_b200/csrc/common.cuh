@@ -45,7 +45,7 @@ void count_launch(int n = 1);
     if (_r != PCLIP_OK) return _r;                                                                    \
   } while (0)
 
-inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+__host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // bump allocator over the caller's workspace
@@ -91,5 +91,13 @@ int tc_rowsumexp(const pclip_clip_fwd_side_t* sides, int n_sides, int D, void* w
 size_t tc_grad_workspace(int64_t Ma, int64_t Nb);
 int tc_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, const float* gscale, void* ws,
             size_t ws_bytes, cudaStream_t st);
+
+// BF16 tcgen05 candidate selection + fp32 re-scoring (topk_tc.cu)
+size_t tc_topk_workspace(int64_t Q, int64_t N, int k);
+int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
+            float* score, int32_t* n_unsafe, void* ws, size_t ws_bytes, cudaStream_t st);
+// exact fp32 top-k on CUDA cores (scores.cu)
+int simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
+              float* score, void* ws, size_t ws_bytes, cudaStream_t st);
 
 }  // namespace pclip

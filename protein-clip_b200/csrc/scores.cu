@@ -263,6 +263,28 @@ int pclip_rank_of_positive(const float* q, const float* bank, const int64_t* pos
   return PCLIP_OK;
 }
 
+size_t pclip_topk_workspace_bytes(int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute) {
+  (void)D;
+  if (compute == PCLIP_COMPUTE_BF16) return tc_topk_workspace(Q, N, k);
+  int nsplit, tps;
+  plan_n_split(Q, N, kMaxK, &nsplit, &tps);
+  return nsplit > 1 ? 2 * align_up((size_t)nsplit * Q * k * sizeof(int64_t), 1024) + 4096 : 0;
+}
+
+int pclip_topk(const float* q, const float* bank, int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute,
+               int64_t index_base, int64_t* idx, float* score, int32_t* n_unsafe, void* workspace,
+               size_t workspace_bytes, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(q && bank && idx && score && Q > 0 && N > 0 && D > 0, PCLIP_ERR_INVALID, "topk: bad argument");
+  PCLIP_REQUIRE(k >= 1 && k <= kMaxK, PCLIP_ERR_UNSUPPORTED, "topk: k must be in [1, %d]", kMaxK);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (compute == PCLIP_COMPUTE_BF16)
+    return tc_topk(q, bank, Q, N, D, k, index_base, idx, score, n_unsafe, workspace, workspace_bytes, st);
+  PCLIP_REQUIRE(compute == PCLIP_COMPUTE_F32, PCLIP_ERR_UNSUPPORTED, "topk: unknown compute mode %d", compute);
+  if (n_unsafe) PCLIP_CHECK_CUDA(cudaMemsetAsync(n_unsafe, 0, sizeof(int32_t), st));
+  return simt_topk(q, bank, Q, N, D, k, index_base, idx, score, workspace, workspace_bytes, st);
+}
+
 int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, int32_t n_lists, int32_t k,
                      int64_t* idx, float* score, pclip_stream_t stream) {
   PCLIP_TRY(require_device());

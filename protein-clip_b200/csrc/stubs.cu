@@ -2,21 +2,6 @@
 #include "common.cuh"
 using namespace pclip;
 extern "C" {
-int pclip_scores(const float*, const float*, int64_t, int64_t, int32_t, int32_t, const float*, float*, pclip_stream_t) {
-  return fail(PCLIP_ERR_UNSUPPORTED, "pclip_scores: not implemented");
-}
-int pclip_rank_of_positive(const float*, const float*, const int64_t*, int64_t, int64_t, int32_t, int32_t*,
-                           pclip_stream_t) {
-  return fail(PCLIP_ERR_UNSUPPORTED, "pclip_rank_of_positive: not implemented");
-}
-size_t pclip_topk_workspace_bytes(int64_t, int64_t, int32_t, int32_t, int32_t) { return 0; }
-int pclip_topk(const float*, const float*, int64_t, int64_t, int32_t, int32_t, int32_t, int64_t, int64_t*, float*,
-               int32_t*, void*, size_t, pclip_stream_t) {
-  return fail(PCLIP_ERR_UNSUPPORTED, "pclip_topk: not implemented");
-}
-int pclip_topk_merge(const int64_t*, const float*, int64_t, int32_t, int32_t, int64_t*, float*, pclip_stream_t) {
-  return fail(PCLIP_ERR_UNSUPPORTED, "pclip_topk_merge: not implemented");
-}
 size_t pclip_filip_workspace_bytes(int64_t, int64_t, int64_t, int64_t, int32_t, int32_t) { return 0; }
 int pclip_filip_fwd(const float*, const float*, const int32_t*, const int32_t*, int64_t, int64_t, int64_t, int64_t,
                     int32_t, const float*, int32_t, float*, float*, int16_t*, int16_t*, void*, size_t, pclip_stream_t) {
@@ -28,3 +13,10 @@ int pclip_filip_bwd(const float*, const float*, const int32_t*, const int32_t*, 
   return fail(PCLIP_ERR_UNSUPPORTED, "pclip_filip_bwd: not implemented");
 }
 }
+namespace pclip {
+size_t tc_topk_workspace(int64_t, int64_t, int) { return 0; }
+int tc_topk(const float*, const float*, int64_t, int64_t, int, int, int64_t, int64_t*, float*, int32_t*, void*, size_t,
+            cudaStream_t) {
+  return fail(PCLIP_ERR_UNSUPPORTED, "pclip_topk: bf16 tensor-core path not implemented");
+}
+}  // namespace pclip

@@ -155,3 +155,99 @@ def clip_loss(x, y, compute: int | None = None) -> torch.Tensor:
     if compute is None:
         compute = default_compute()
     return _ClipInfoNCE.apply(len(xs), compute, *xs, *ys)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Staged CLIP step with caller-owned buffers: pack -> row/column sum-exp -> finalize -> gradients.
+# The same stages pclip_clip_loss runs internally, exposed one by one so that (a) a row-sharded job can put
+# its all-gather between `pack` and `rowsumexp` (pclip/sharded.py) and (b) bench.py can bracket the dominant
+# kernel with CUDA events inside the timed region.  No allocation happens after construction.
+# ---------------------------------------------------------------------------------------------------------
+class ClipPlan:
+    """Buffers and stage calls for S = A Bfull^T with `Ma` local rows per modality against `Nb` gathered rows.
+
+    Single GPU: Ma == Nb == B, diag_offset == 0.  Row-sharded: Ma = B / P, Nb = B, diag_offset = rank * Ma."""
+
+    def __init__(self, Ma: int, Nb: int, D: int, compute: int, device, diag_offset: int = 0):
+        self.Ma, self.Nb, self.D, self.compute, self.dev, self.off = Ma, Nb, D, compute, torch.device(device), diag_offset
+        tc = compute == BF16
+        self.cdt = torch.bfloat16 if tc else torch.float32
+        self.ldT = (Nb + 63) // 64 * 64
+        dev = self.dev
+        f32 = dict(dtype=torch.float32, device=dev)
+        # local packed rows of both modalities, and the full (gathered) matrices; on one GPU they alias
+        self.xl = torch.empty(Ma, D, dtype=self.cdt, device=dev)
+        self.yl = torch.empty(Ma, D, dtype=self.cdt, device=dev)
+        self.local_is_full = Ma == Nb
+        self.xf = self.xl if self.local_is_full else torch.empty(Nb, D, dtype=self.cdt, device=dev)
+        self.yf = self.yl if self.local_is_full else torch.empty(Nb, D, dtype=self.cdt, device=dev)
+        self.xfT = torch.zeros(D, self.ldT, dtype=self.cdt, device=dev) if tc else None
+        self.yfT = torch.zeros(D, self.ldT, dtype=self.cdt, device=dev) if tc else None
+        self.rowsum, self.colsum = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
+        self.diag, self.diag2 = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
+        self.row_lse, self.col_lse = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
+        self.rinv, self.cinv = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
+        # 1/R and 1/C of ALL rows (the gradient kernel needs the other side's normalisers for every column)
+        self.rinv_f = self.rinv if self.local_is_full else torch.empty(Nb, **f32)
+        self.cinv_f = self.cinv if self.local_is_full else torch.empty(Nb, **f32)
+        self.loss = torch.zeros(1, **f32)
+        self.dx, self.dy = torch.empty(Ma, D, **f32), torch.empty(Ma, D, **f32)
+        lib = L.lib()
+        n = max(lib.pclip_clip_rowsumexp_workspace_bytes(Ma, Nb, D, compute),
+                lib.pclip_clip_grad_workspace_bytes(Ma, Nb, D, compute), 1024)
+        self.ws_bytes = int(n)
+        self._ws_owner, self.ws = L.workspace(n, dev)
+
+    def _st(self):
+        return L.stream_ptr(self.dev)
+
+    def pack(self, xs, ys):
+        """Strided row chunks (GradCache leaves, `.t()` views) -> packed compute-dtype rows (+ transposes)."""
+        lib = L.lib()
+        xs, ys = _as_rows(xs), _as_rows(ys)
+        full = self.local_is_full
+        for src, out, outT in ((xs, self.xl, self.xfT if full else None), (ys, self.yl, self.yfT if full else None)):
+            L.check(lib.pclip_pack(L.chunks_of(src), len(src), L.dtype_code(src[0].dtype), self.Ma, self.D,
+                                   L.dtype_code(self.cdt), L.ptr(out), L.ptr(outT), self.ldT, self._st()))
+
+    def transpose_full(self):
+        """After an all-gather into xf / yf: the transposed copies the bf16 gradient kernel reads."""
+        if self.compute != BF16 or self.local_is_full:
+            return
+        lib = L.lib()
+        for src, dst in ((self.xf, self.xfT), (self.yf, self.yfT)):
+            L.check(lib.pclip_transpose_bf16(L.ptr(src), self.Nb, self.D, L.ptr(dst), self.ldT, self._st()))
+
+    def rowsumexp(self):
+        sides = (L.FwdSide * 2)(
+            L.FwdSide(L.ptr(self.xl), L.ptr(self.yf), self.Ma, self.Nb, self.off, L.ptr(self.rowsum), L.ptr(self.diag)),
+            L.FwdSide(L.ptr(self.yl), L.ptr(self.xf), self.Ma, self.Nb, self.off, L.ptr(self.colsum), L.ptr(self.diag2)))
+        L.check(L.lib().pclip_clip_rowsumexp(sides, 2, self.D, self.compute, self.ws, self.ws_bytes, self._st()))
+
+    def finalize(self, B_total: int):
+        """loss[0] = 1/(2B) sum_i (log R_i + log C_i - 2 S_ii) over the local rows; 1/R, 1/C for the backward."""
+        L.check(L.lib().pclip_clip_finalize(L.ptr(self.rowsum), L.ptr(self.colsum), L.ptr(self.diag), self.Ma,
+                                            0.5 / B_total, L.ptr(self.row_lse), L.ptr(self.col_lse), L.ptr(self.rinv),
+                                            L.ptr(self.cinv), L.ptr(self.loss), self._st()))
+
+    def grad(self, B_total: int, gscale: torch.Tensor | None = None):
+        sides = (L.BwdSide * 2)(
+            L.BwdSide(L.ptr(self.xl), L.ptr(self.yf), L.ptr(self.yfT), self.ldT, self.Ma, self.Nb, self.off,
+                      L.ptr(self.rinv), L.ptr(self.cinv_f), L.ptr(self.dx)),
+            L.BwdSide(L.ptr(self.yl), L.ptr(self.xf), L.ptr(self.xfT), self.ldT, self.Ma, self.Nb, self.off,
+                      L.ptr(self.cinv), L.ptr(self.rinv_f), L.ptr(self.dy)))
+        L.check(L.lib().pclip_clip_grad(sides, 2, self.D, self.compute, 0.5 / B_total, L.ptr(gscale), self.ws,
+                                        self.ws_bytes, self._st()))
+
+    def step(self, xs, ys, events=None):
+        """Single-GPU fwd + bwd.  `events`: optional dict name -> (start, end) torch.cuda.Event pairs to record
+        around the stages on the current stream (bench.py's roofline legs)."""
+        def rec(name, i):
+            if events is not None and name in events:
+                events[name][i].record(torch.cuda.current_stream(self.dev))
+        assert self.local_is_full
+        rec("pack", 0); self.pack(xs, ys); rec("pack", 1)
+        rec("rowsumexp", 0); self.rowsumexp(); rec("rowsumexp", 1)
+        self.finalize(self.Nb)
+        rec("grad", 0); self.grad(self.Nb); rec("grad", 1)
+        return self.loss, self.dx, self.dy

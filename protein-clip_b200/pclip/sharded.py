@@ -1,0 +1,58 @@
+"""Row-sharded CLIP InfoNCE over the GPUs of one box (BASELINE.json configs[3]).
+
+Rank p owns rows [p*B/P, (p+1)*B/P) of BOTH modalities.  One step:
+
+  1. pack local rows to the compute dtype                                   (kernel, local)
+  2. all-gather X and Y over NCCL / NVLink                                   (2 x B*D*2 bytes in bf16)
+  3. row sums  R_i = sum_j exp(x_i . y_j)  for local i against ALL y, and
+     col sums  C_i = sum_j exp(y_i . x_j)  for local i against ALL x          (kernel, local, complete)
+  4. loss partial -> all-reduce of one float; all-gather of 1/R and 1/C       (2 x B floats)
+  5. dX_local = sum_j P_ij y_j  and  dY_local = sum_j P_ji x_j               (kernel, local, complete)
+
+Because every rank evaluates both the (X_p, Y) and the (Y_p, X) side, each gradient row block is complete locally:
+there is NO gradient exchange (the price is that the score tiles of the two sides are both computed, which the
+single-GPU path does as well).  The collective calls go through torch.distributed (plumbing); the arithmetic is
+all in libpclip.so via the `stages` object (pclip.ops.ClipPlan on CUDA).  The stages object is injectable only so
+that tests/test_sharded_gloo.py can drive this host logic on CPU ranks over gloo with the oracle as the stage
+backend; the product constructs ClipPlan and nothing else.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+class ShardedClip:
+    def __init__(self, B: int, D: int, compute: int, device, group=None, stages=None):
+        self.group = group
+        self.P = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if B % self.P:
+            raise ValueError(f"B = {B} must divide evenly over {self.P} ranks")
+        self.B, self.D, self.Ma = B, D, B // self.P
+        if stages is None:
+            from .ops import ClipPlan
+            stages = ClipPlan(self.Ma, B, D, compute, device, diag_offset=self.rank * self.Ma)
+        self.s = stages
+
+    def step(self, xs, ys, gscale=None, events=None):
+        """xs / ys: this rank's row chunks.  Returns (global loss [1], dX_local [Ma, D], dY_local [Ma, D])."""
+        s, g = self.s, self.group
+
+        def rec(name, i):
+            if events is not None and name in events:
+                events[name][i].record(torch.cuda.current_stream(s.dev))
+
+        s.pack(xs, ys)
+        if self.P > 1:
+            dist.all_gather_into_tensor(s.xf, s.xl, group=g)
+            dist.all_gather_into_tensor(s.yf, s.yl, group=g)
+        s.transpose_full()
+        rec("rowsumexp", 0); s.rowsumexp(); rec("rowsumexp", 1)
+        s.finalize(self.B)
+        if self.P > 1:
+            dist.all_reduce(s.loss, group=g)
+            dist.all_gather_into_tensor(s.rinv_f, s.rinv, group=g)
+            dist.all_gather_into_tensor(s.cinv_f, s.cinv, group=g)
+        rec("grad", 0); s.grad(self.B, gscale); rec("grad", 1)
+        return s.loss, s.dx, s.dy
