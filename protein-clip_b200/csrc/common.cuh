@@ -97,7 +97,10 @@ size_t tc_topk_workspace(int64_t Q, int64_t N, int k);
 int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
             float* score, int32_t* n_unsafe, void* ws, size_t ws_bytes, cudaStream_t st);
 // exact fp32 top-k on CUDA cores (scores.cu)
+// qlist / qcount (device, optional): "list mode" -- only queries qlist[0 .. *qcount) are recomputed, in place
+size_t simt_topk_workspace(int64_t Q, int64_t N, int k, bool list_mode);
 int simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
-              float* score, void* ws, size_t ws_bytes, cudaStream_t st);
+              float* score, void* ws, size_t ws_bytes, cudaStream_t st, const int32_t* qlist = nullptr,
+              const int32_t* qcount = nullptr);
 
 }  // namespace pclip

@@ -98,7 +98,12 @@ constexpr int kMaxK = 64;
 __global__ void __launch_bounds__(256) topk_kernel(const float* __restrict__ q, const float* __restrict__ bank,
                                                    int64_t Q, int64_t N, int D, int k, int tiles_per_split,
                                                    int64_t index_base, int64_t* __restrict__ idx_out,
-                                                   float* __restrict__ score_out) {
+                                                   float* __restrict__ score_out, const int32_t* __restrict__ qlist,
+                                                   const int32_t* __restrict__ qcount) {
+  // list mode (qlist != NULL): logical row r is query qlist[r]; only the first *qcount logical rows exist.
+  const int64_t Qstride = Q;
+  if (qcount) Q = *qcount;
+  if ((int64_t)blockIdx.x * kBM >= Q) return;
   extern __shared__ __align__(16) uint8_t dyn[];
   float(*As)[kBM + kPad] = reinterpret_cast<float(*)[kBM + kPad]>(dyn);
   float(*Bs)[kBN + kPad] = As + kBK;
@@ -114,7 +119,7 @@ __global__ void __launch_bounds__(256) topk_kernel(const float* __restrict__ q, 
   float acc[4][4];
   for (int64_t t = t0; t < t1; ++t) {
     const int64_t col0 = t * kBN;
-    score_tile(q, bank, Q, N, D, row0, col0, As, Bs, acc);
+    score_tile(q, bank, Q, N, D, row0, col0, As, Bs, acc, qlist);
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -142,7 +147,7 @@ __global__ void __launch_bounds__(256) topk_kernel(const float* __restrict__ q, 
   }
   if (tid < kBM && row0 + tid < Q) {
     const int64_t r = row0 + tid;
-    const int64_t o = ((int64_t)blockIdx.y * Q + r) * k;
+    const int64_t o = ((int64_t)blockIdx.y * Qstride + r) * k;
     for (int p = 0; p < k; ++p) {
       const bool have = p < filled;
       idx_out[o + p] = have ? lidx[tid * kMaxK + p] + index_base : -1;
@@ -153,9 +158,11 @@ __global__ void __launch_bounds__(256) topk_kernel(const float* __restrict__ q, 
 
 // merge n_lists sorted candidate lists per query: lists laid out [n_lists][Q][k]; (score desc, index asc)
 __global__ void topk_merge_kernel(const int64_t* __restrict__ idx_in, const float* __restrict__ score_in, int64_t Q,
-                                  int n_lists, int k, int64_t* __restrict__ idx, float* __restrict__ score) {
+                                  int n_lists, int k, int64_t* __restrict__ idx, float* __restrict__ score,
+                                  const int32_t* __restrict__ qlist, const int32_t* __restrict__ qcount) {
   const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (r >= Q) return;
+  if (r >= (qcount ? (int64_t)*qcount : Q)) return;
+  const int64_t wr = qlist ? (int64_t)qlist[r] : r;  // where the merged row is written
   int head[kMaxK];
   for (int l = 0; l < n_lists; ++l) head[l] = 0;
   for (int p = 0; p < k; ++p) {
@@ -175,11 +182,11 @@ __global__ void topk_merge_kernel(const int64_t* __restrict__ idx_in, const floa
       }
     }
     if (best < 0) {
-      idx[r * k + p] = -1;
-      score[r * k + p] = -FLT_MAX;
+      idx[wr * k + p] = -1;
+      score[wr * k + p] = -FLT_MAX;
     } else {
-      idx[r * k + p] = bi;
-      score[r * k + p] = bs;
+      idx[wr * k + p] = bi;
+      score[wr * k + p] = bs;
       ++head[best];
     }
   }
@@ -199,20 +206,27 @@ static size_t topk_smem_bytes() {
   return sizeof(float) * (2 * kBK * (kBM + kPad) + kBM * (kBN + 1) + kBM * kMaxK) + sizeof(int64_t) * kBM * kMaxK;
 }
 
-int simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
-              float* score, void* ws, size_t ws_bytes, cudaStream_t st);
-
 }  // namespace pclip
 
 using namespace pclip;
 
-int pclip::simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base,
-                     int64_t* idx, float* score, void* ws, size_t ws_bytes, cudaStream_t st) {
+size_t pclip::simt_topk_workspace(int64_t Q, int64_t N, int k, bool list_mode) {
   int nsplit, tps;
-  plan_n_split(Q, N, kMaxK, &nsplit, &tps);
+  plan_n_split(list_mode ? 64 : Q, N, kMaxK, &nsplit, &tps);
+  if (nsplit == 1 && !list_mode) return 0;
+  return align_up((size_t)nsplit * Q * k * sizeof(int64_t), 1024) + align_up((size_t)nsplit * Q * k * sizeof(float), 1024) +
+         4096;
+}
+
+int pclip::simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base,
+                     int64_t* idx, float* score, void* ws, size_t ws_bytes, cudaStream_t st, const int32_t* qlist,
+                     const int32_t* qcount) {
+  int nsplit, tps;
+  // list mode: the number of live rows is only known on the device; plan the bank split for a handful of rows
+  plan_n_split(qlist ? 64 : Q, N, kMaxK, &nsplit, &tps);
   int64_t* pidx = idx;
   float* pscore = score;
-  if (nsplit > 1) {
+  if (nsplit > 1 || qlist) {
     Workspace w(ws, ws_bytes);
     PCLIP_REQUIRE(ws, PCLIP_ERR_WORKSPACE, "topk: workspace required");
     pidx = w.take<int64_t>((size_t)nsplit * Q * k);
@@ -222,10 +236,11 @@ int pclip::simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, in
   const size_t smem = topk_smem_bytes();
   PCLIP_CHECK_CUDA(cudaFuncSetAttribute(topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)ceil_div(Q, kBM), (unsigned)nsplit);
-  topk_kernel<<<grid, 256, smem, st>>>(q, bank, Q, N, D, k, tps, index_base, pidx, pscore);
+  topk_kernel<<<grid, 256, smem, st>>>(q, bank, Q, N, D, k, tps, index_base, pidx, pscore, qlist, qcount);
   PCLIP_CHECK_LAUNCH();
-  if (nsplit > 1) {
-    topk_merge_kernel<<<(unsigned)ceil_div(Q, 128), 128, 0, st>>>(pidx, pscore, Q, nsplit, k, idx, score);
+  if (nsplit > 1 || qlist) {
+    topk_merge_kernel<<<(unsigned)ceil_div(Q, 128), 128, 0, st>>>(pidx, pscore, Q, nsplit, k, idx, score, qlist,
+                                                                  qcount);
     PCLIP_CHECK_LAUNCH();
   }
   return PCLIP_OK;
@@ -266,9 +281,7 @@ int pclip_rank_of_positive(const float* q, const float* bank, const int64_t* pos
 size_t pclip_topk_workspace_bytes(int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute) {
   (void)D;
   if (compute == PCLIP_COMPUTE_BF16) return tc_topk_workspace(Q, N, k);
-  int nsplit, tps;
-  plan_n_split(Q, N, kMaxK, &nsplit, &tps);
-  return nsplit > 1 ? 2 * align_up((size_t)nsplit * Q * k * sizeof(int64_t), 1024) + 4096 : 0;
+  return simt_topk_workspace(Q, N, k, false);
 }
 
 int pclip_topk(const float* q, const float* bank, int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute,
@@ -291,8 +304,8 @@ int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, in
   PCLIP_REQUIRE(idx_in && score_in && idx && score && Q > 0, PCLIP_ERR_INVALID, "topk_merge: bad argument");
   PCLIP_REQUIRE(n_lists >= 1 && n_lists <= kMaxK && k >= 1 && k <= kMaxK, PCLIP_ERR_UNSUPPORTED,
                 "topk_merge: n_lists and k must be in [1, %d]", kMaxK);
-  topk_merge_kernel<<<(unsigned)ceil_div(Q, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(idx_in, score_in, Q,
-                                                                                              n_lists, k, idx, score);
+  topk_merge_kernel<<<(unsigned)ceil_div(Q, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      idx_in, score_in, Q, n_lists, k, idx, score, nullptr, nullptr);
   PCLIP_CHECK_LAUNCH();
   return PCLIP_OK;
 }

@@ -9,9 +9,11 @@ namespace pclip {
 constexpr int kBM = 64, kBN = 64, kBK = 16, kPad = 4;
 
 // acc[i][j] += sum_k a[row0 + ty*4+i, k] * b[col0 + tx*4+j, k]   (k ascending)
+// rowmap (optional): logical row r of `a` lives at physical row rowmap[r] (Ma counts logical rows)
 __device__ __forceinline__ void score_tile(const float* __restrict__ a, const float* __restrict__ b, int64_t Ma,
                                            int64_t Nb, int D, int64_t row0, int64_t col0, float (*As)[kBM + kPad],
-                                           float (*Bs)[kBN + kPad], float (&acc)[4][4]) {
+                                           float (*Bs)[kBN + kPad], float (&acc)[4][4],
+                                           const int32_t* __restrict__ rowmap = nullptr) {
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
 #pragma unroll
@@ -24,7 +26,7 @@ __device__ __forceinline__ void score_tile(const float* __restrict__ a, const fl
       const int idx = tid + t * 256;
       const int r = idx >> 4, k = idx & 15;
       const int64_t gr = row0 + r, gc = col0 + r;
-      As[k][r] = (gr < Ma && k0 + k < D) ? a[gr * D + k0 + k] : 0.f;
+      As[k][r] = (gr < Ma && k0 + k < D) ? a[(rowmap ? (int64_t)rowmap[gr] : gr) * D + k0 + k] : 0.f;
       Bs[k][r] = (gc < Nb && k0 + k < D) ? b[gc * D + k0 + k] : 0.f;
     }
     __syncthreads();

@@ -13,10 +13,3 @@ int pclip_filip_bwd(const float*, const float*, const int32_t*, const int32_t*, 
   return fail(PCLIP_ERR_UNSUPPORTED, "pclip_filip_bwd: not implemented");
 }
 }
-namespace pclip {
-size_t tc_topk_workspace(int64_t, int64_t, int) { return 0; }
-int tc_topk(const float*, const float*, int64_t, int64_t, int, int, int64_t, int64_t*, float*, int32_t*, void*, size_t,
-            cudaStream_t) {
-  return fail(PCLIP_ERR_UNSUPPORTED, "pclip_topk: bf16 tensor-core path not implemented");
-}
-}  // namespace pclip

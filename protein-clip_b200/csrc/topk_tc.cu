@@ -1,0 +1,437 @@
+// Cosine / dot-product top-k retrieval on the tensor cores (PCLIP_COMPUTE_BF16).
+//   ref: modules/training_utils.py:219-222 (rank of the positive among the candidates), topk.py:47-61 (top-k accuracy);
+//   generalised to "top-k of N bank rows for each of Q queries" (BASELINE.json configs[4]).
+//
+// Three stages:
+//   1. to_bf16_norm_kernel   fp32 rows -> bf16 rows (+ row norms, + max bank norm)          HBM-bound pre-pass
+//   2. tc_topk_kernel        each CTA keeps 256 queries resident (two 128-row UMMA A tiles), streams the bank through a
+//                            TMA ring, scores 128-column tiles with tcgen05.mma into four TMEM accumulators
+//                            (2 query tiles x double buffer) and filters them in the epilogue: thread == query row,
+//                            register threshold, sorted candidate list (kc >= k + margin entries) in shared memory.
+//   3. topk_rescore_kernel   candidates are re-scored with the fp32 FFMA chain of the exact path (bit-identical to
+//                            PCLIP_COMPUTE_F32), sorted (score desc, index asc) and cut to k.  A query is PROVEN exact
+//                            when its k-th fp32 score exceeds (largest discarded bf16 score + eps_q), eps_q being a
+//                            rigorous bound of |bf16 score - fp32 score|; otherwise it is appended to a list that the
+//                            exact fp32 kernel (scores.cu, list mode) recomputes.  No host synchronisation anywhere.
+#include <cuda_bf16.h>
+#include <float.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace pclip {
+
+namespace tk {
+constexpr int kTile = 128;
+constexpr int kDim = 128;
+constexpr uint32_t kPanelBytes = 128 * 128;
+constexpr uint32_t kTileBytes = 2 * kPanelBytes;
+constexpr int kQTiles = 2;              // query tiles per CTA (256 queries): halves the bank traffic per score
+constexpr int kRows = kQTiles * kTile;
+constexpr int kStages = 3;              // bank ring
+constexpr int kMaxCand = 32;            // candidate list capacity per query
+constexpr int kThreads = 64 + 32 * 4 * kQTiles;  // TMA warp, MMA warp, 8 epilogue warps
+constexpr int kEpiThreadsPerTile = 128;
+// smem: A (2 tiles) | B ring | candidate scores [kMaxCand][256] | candidate idx [kMaxCand][256] | barriers
+constexpr uint32_t kSmemBytes = kTileBytes * (kQTiles + kStages) + kMaxCand * kRows * 8 + 256 + 1024;
+static_assert(kSmemBytes <= 232448, "shared memory budget");
+
+__device__ __forceinline__ uint64_t tile_desc(uint32_t tile_smem_addr, int k) {
+  const uint32_t addr = tile_smem_addr + (uint32_t)(k >> 2) * kPanelBytes + (uint32_t)(k & 3) * 32u;
+  return make_smem_desc_sw128(addr, 16, 1024);
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+}  // namespace tk
+
+// ---------------------------------------------------------------------------------------------------------
+// 1. fp32 [rows, 128] -> bf16 [rows, 128]; norm[r] = ||row r||_2 (optional); *maxnorm = max_r ||row r|| (optional,
+//    as an int-ordered float: norms are >= 0).  One warp per row, one float4 per lane.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) to_bf16_norm_kernel(const float* __restrict__ in, int64_t rows,
+                                                           __nv_bfloat16* __restrict__ out, float* __restrict__ norm,
+                                                           int* __restrict__ maxnorm_bits) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  float wmax = 0.f;
+  for (int64_t r = warp0; r < rows; r += nwarps) {
+    const float4 v = *reinterpret_cast<const float4*>(in + r * tk::kDim + lane * 4);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(out + r * tk::kDim + lane * 4) = pk;
+    float s = v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float n = sqrtf(s);
+    if (norm && lane == 0) norm[r] = n;
+    wmax = fmaxf(wmax, n);
+  }
+  if (maxnorm_bits && lane == 0 && wmax > 0.f) atomicMax(maxnorm_bits, __float_as_int(wmax));
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// 2. candidate selection
+// ---------------------------------------------------------------------------------------------------------
+struct TopkArgs {
+  int64_t Q, N;
+  int kc;               // candidates kept per (query, bank split)
+  int tiles_per_split;  // bank tiles (of 128 rows) per blockIdx.y
+  int32_t* cand_idx;    // [nsplit][Q][kc]   bank row (local to this call), -1 = empty slot
+  float* cand_score;    // [nsplit][Q][kc]   bf16-path score
+};
+
+__global__ void __launch_bounds__(tk::kThreads, 1)
+tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tb, const TopkArgs args) {
+  using namespace tk;
+  const int64_t row0 = (int64_t)blockIdx.x * kRows;
+  const int ntiles_all = (int)((args.N + kTile - 1) / kTile);
+  const int tile_begin = blockIdx.y * args.tiles_per_split;
+  const int tile_end = min(tile_begin + args.tiles_per_split, ntiles_all);
+  const int ntiles = max(tile_end - tile_begin, 0);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_tiles = smem;
+  uint8_t* b_tiles = a_tiles + kQTiles * kTileBytes;
+  float* ls = reinterpret_cast<float*>(b_tiles + kStages * kTileBytes);   // [kMaxCand][kRows]
+  int32_t* li = reinterpret_cast<int32_t*>(ls + kMaxCand * kRows);        // [kMaxCand][kRows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(li + kMaxCand * kRows);
+  uint64_t* a_full = bars;                       // 1
+  uint64_t* b_full = a_full + 1;                 // kStages
+  uint64_t* b_empty = b_full + kStages;          // kStages
+  uint64_t* t_full = b_empty + kStages;          // [kQTiles][2]
+  uint64_t* t_empty = t_full + 2 * kQTiles;      // [kQTiles][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2 * kQTiles);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    mbar_init(a_full, 1);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&b_full[i], 1);
+      mbar_init(&b_empty[i], 1);
+    }
+    for (int i = 0; i < 2 * kQTiles; ++i) {
+      mbar_init(&t_full[i], 1);
+      mbar_init(&t_empty[i], kEpiThreadsPerTile);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tq);
+      tma_prefetch_desc(&tb);
+      mbar_arrive_expect_tx(a_full, kQTiles * kTileBytes);
+      for (int h = 0; h < kQTiles; ++h) {
+        tma_load_2d(a_tiles + h * kTileBytes, &tq, a_full, 0, (int32_t)(row0 + h * kTile));
+        tma_load_2d(a_tiles + h * kTileBytes + kPanelBytes, &tq, a_full, 64, (int32_t)(row0 + h * kTile));
+      }
+      for (int t = 0; t < ntiles; ++t) {
+        const int stage = t % kStages;
+        const uint32_t phase = (uint32_t)(t / kStages) & 1u;
+        mbar_wait(&b_empty[stage], phase ^ 1u);
+        mbar_arrive_expect_tx(&b_full[stage], kTileBytes);
+        const int32_t col0 = (tile_begin + t) * kTile;
+        uint8_t* dst = b_tiles + (size_t)stage * kTileBytes;
+        tma_load_2d(dst, &tb, &b_full[stage], 0, col0);
+        tma_load_2d(dst + kPanelBytes, &tb, &b_full[stage], 64, col0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(kTile, kTile, 0, 0);
+      mbar_wait(a_full, 0);
+      for (int t = 0; t < ntiles; ++t) {
+        const int stage = t % kStages;
+        const uint32_t phase = (uint32_t)(t / kStages) & 1u;
+        const int buf = t & 1;
+        const uint32_t bphase = (uint32_t)(t >> 1) & 1u;
+        mbar_wait(&b_full[stage], phase);
+        const uint32_t b_addr = smem_u32(b_tiles + (size_t)stage * kTileBytes);
+#pragma unroll
+        for (int h = 0; h < kQTiles; ++h) {
+          mbar_wait(&t_empty[h * 2 + buf], bphase ^ 1u);
+          tc_fence_after_sync();
+          const uint32_t a_addr = smem_u32(a_tiles + h * kTileBytes);
+          const uint32_t d = tmem_base + (uint32_t)(h * 2 + buf) * kTile;
+#pragma unroll
+          for (int k = 0; k < kDim / 16; ++k)
+            umma_bf16_ss(d, tile_desc(a_addr, k), tile_desc(b_addr, k), idesc, k > 0 ? 1u : 0u);
+          umma_commit(&t_full[h * 2 + buf]);
+        }
+        umma_commit(&b_empty[stage]);
+      }
+    }
+  } else {
+    // ---- epilogue: thread == query row; candidate list columns of shared memory are private to the thread ----
+    const int h = (warp - 2) >> 2;   // query tile
+    const int q = warp & 3;          // TMEM lane quadrant this warp may read
+    const int lrow = h * kTile + q * 32 + lane;
+    float* my_s = ls + lrow;         // element j at my_s[j * kRows]
+    int32_t* my_i = li + lrow;
+    const int kc = args.kc;
+    int cnt = 0;
+    float thr = -FLT_MAX;            // kc-th best so far once the list is full
+    for (int t = 0; t < ntiles; ++t) {
+      const int buf = t & 1;
+      const uint32_t bphase = (uint32_t)(t >> 1) & 1u;
+      const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
+      const bool ragged = col0 + kTile > args.N;
+      mbar_wait(&t_full[h * 2 + buf], bphase);
+      tc_fence_after_sync();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 2 + buf) * kTile;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        if (ragged) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e)
+            if (col0 + c * 32 + e >= args.N) r[e] = __float_as_uint(-FLT_MAX);  // TMA zero-filled rows beyond N
+        }
+        float m = -FLT_MAX;
+#pragma unroll
+        for (int e = 0; e < 32; e += 2) m = max3(m, __uint_as_float(r[e]), __uint_as_float(r[e + 1]));
+        if (m > thr || cnt < kc) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const float v = __uint_as_float(r[e]);
+            if ((v > thr || cnt < kc) && v > -FLT_MAX) {
+              // sorted insert (descending); an equal score stays behind earlier (lower-index) entries
+              int p = cnt < kc ? cnt : kc - 1;
+              while (p > 0 && my_s[(p - 1) * kRows] < v) {
+                my_s[p * kRows] = my_s[(p - 1) * kRows];
+                my_i[p * kRows] = my_i[(p - 1) * kRows];
+                --p;
+              }
+              my_s[p * kRows] = v;
+              my_i[p * kRows] = (int32_t)(col0 + c * 32 + e);
+              if (cnt < kc) ++cnt;
+              if (cnt == kc) thr = my_s[(kc - 1) * kRows];
+            }
+          }
+        }
+      }
+      tc_fence_before_sync();
+      mbar_arrive(&t_empty[h * 2 + buf]);
+    }
+    const int64_t row = row0 + lrow;
+    if (row < args.Q) {
+      const int64_t o = ((int64_t)blockIdx.y * args.Q + row) * kc;
+      for (int j = 0; j < kc; ++j) {
+        args.cand_idx[o + j] = j < cnt ? my_i[j * kRows] : -1;
+        args.cand_score[o + j] = j < cnt ? my_s[j * kRows] : -FLT_MAX;
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    __syncwarp();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// 3. exact re-scoring of the candidates + proof of exactness.  One warp per query.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kRescoreWarps = 8;
+constexpr int kMaxCandTotal = 512;  // nsplit * kc
+
+__global__ void __launch_bounds__(kRescoreWarps * 32)
+topk_rescore_kernel(const float* __restrict__ q, const float* __restrict__ bank, const int32_t* __restrict__ cand_idx,
+                    const float* __restrict__ cand_score, const float* __restrict__ qnorm,
+                    const int* __restrict__ bmax_bits, int64_t Q, int nsplit, int kc, int k, int64_t index_base,
+                    int64_t* __restrict__ idx_out, float* __restrict__ score_out, int32_t* __restrict__ unsafe_list,
+                    int32_t* __restrict__ unsafe_count) {
+  __shared__ float qs[kRescoreWarps][tk::kDim];
+  __shared__ float cs[kRescoreWarps][kMaxCandTotal];
+  __shared__ int32_t ci[kRescoreWarps][kMaxCandTotal];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * kRescoreWarps + w;
+  if (row >= Q) return;
+  const int M = nsplit * kc;
+  *reinterpret_cast<float4*>(&qs[w][lane * 4]) = *reinterpret_cast<const float4*>(q + row * tk::kDim + lane * 4);
+  __syncwarp();
+  float tdisc = -FLT_MAX;  // largest bf16 score any discarded bank row can have
+  for (int c = lane; c < M; c += 32) {
+    const int s = c / kc, j = c - s * kc;
+    const int64_t o = ((int64_t)s * Q + row) * kc + j;
+    const int32_t id = cand_idx[o];
+    float acc = -FLT_MAX;
+    if (id >= 0) {
+      const float* b = bank + (int64_t)id * tk::kDim;
+      acc = 0.f;
+#pragma unroll 4
+      for (int d = 0; d < tk::kDim; d += 4) {  // the exact path's chain: ascending d, one FFMA per element
+        const float4 bv = *reinterpret_cast<const float4*>(b + d);
+        acc = fmaf(qs[w][d], bv.x, acc);
+        acc = fmaf(qs[w][d + 1], bv.y, acc);
+        acc = fmaf(qs[w][d + 2], bv.z, acc);
+        acc = fmaf(qs[w][d + 3], bv.w, acc);
+      }
+      if (j == kc - 1) tdisc = fmaxf(tdisc, cand_score[o]);  // this split's list is full: its tail bounds the rest
+    }
+    cs[w][c] = acc;
+    ci[w][c] = id >= 0 ? id : 0x7fffffff;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) tdisc = fmaxf(tdisc, __shfl_xor_sync(0xffffffffu, tdisc, o));
+  __syncwarp();
+  float kth = FLT_MAX;
+  bool have_k = true;
+  for (int p = 0; p < k; ++p) {
+    float bs = -FLT_MAX;
+    int32_t bi = 0x7fffffff;
+    int bc = -1;
+    for (int c = lane; c < M; c += 32) {
+      const float s = cs[w][c];
+      const int32_t id = ci[w][c];
+      if (id != 0x7fffffff && (bc < 0 || s > bs || (s == bs && id < bi))) {
+        bs = s;
+        bi = id;
+        bc = c;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float os = __shfl_xor_sync(0xffffffffu, bs, o);
+      const int32_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+      if (oc >= 0 && (bc < 0 || os > bs || (os == bs && oi < bi))) {
+        bs = os;
+        bi = oi;
+        bc = oc;
+      }
+    }
+    if (bc >= 0 && (bc & 31) == lane) ci[w][bc] = 0x7fffffff;  // taken
+    __syncwarp();
+    if (lane == 0) {
+      idx_out[row * k + p] = bc >= 0 ? (int64_t)bi + index_base : -1;
+      score_out[row * k + p] = bc >= 0 ? bs : -FLT_MAX;
+    }
+    if (bc >= 0) kth = bs; else have_k = false;
+  }
+  if (lane == 0 && tdisc > -FLT_MAX) {
+    // |bf16-path score - fp32-chain score| <= (2^-8 (1 + 2^-9) + D 2^-23) ||q|| ||b||  (bf16 RN of both operands,
+    // fp32 accumulation on both sides); 1.02 covers the second-order terms.
+    const float eps = (0.00390625f * 1.02f + 128.0f * 1.1920929e-7f) * qnorm[row] * __int_as_float(*bmax_bits);
+    if (!have_k || !(kth > tdisc + eps)) unsafe_list[atomicAdd(unsafe_count, 1)] = (int32_t)row;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------
+static int cand_per_query(int k) { return std::min(tk::kMaxCand, std::max(16, 2 * k + 4)); }
+
+static void plan_topk_split(int64_t Q, int64_t N, int kc, int* nsplit, int* tps) {
+  const int64_t rb = ceil_div(Q, tk::kRows), nt = ceil_div(N, tk::kTile);
+  int64_t want = ceil_div(148, rb);
+  want = std::min<int64_t>(want, kMaxCandTotal / kc);
+  want = std::max<int64_t>(1, std::min(want, nt));
+  *tps = (int)ceil_div(nt, want);
+  *nsplit = (int)ceil_div(nt, *tps);
+}
+
+struct TopkWs {
+  __nv_bfloat16 *qb, *bb;
+  float* qnorm;
+  int32_t* scalars;  // [0] max bank norm bits, [1] unsafe count
+  int32_t* unsafe;
+  int32_t* cand_idx;
+  float* cand_score;
+  void* fix;
+  size_t fix_bytes;
+  bool ok;
+};
+
+static TopkWs carve(void* ws, size_t ws_bytes, int64_t Q, int64_t N, int k, int kc, int nsplit) {
+  Workspace w(ws, ws_bytes);
+  TopkWs t;
+  t.qb = w.take<__nv_bfloat16>((size_t)(Q + tk::kRows) * tk::kDim);
+  t.bb = w.take<__nv_bfloat16>((size_t)(N + tk::kTile) * tk::kDim);
+  t.qnorm = w.take<float>(Q);
+  t.scalars = w.take<int32_t>(2);
+  t.unsafe = w.take<int32_t>(Q);
+  t.cand_idx = w.take<int32_t>((size_t)nsplit * Q * kc);
+  t.cand_score = w.take<float>((size_t)nsplit * Q * kc);
+  t.fix_bytes = simt_topk_workspace(Q, N, k, true);
+  t.fix = w.take<char>(t.fix_bytes);
+  t.ok = ws != nullptr && w.ok();
+  return t;
+}
+
+size_t tc_topk_workspace(int64_t Q, int64_t N, int k) {
+  const int kc = cand_per_query(k);
+  int nsplit, tps;
+  plan_topk_split(Q, N, kc, &nsplit, &tps);
+  Workspace w(nullptr, 0);
+  w.take<__nv_bfloat16>((size_t)(Q + tk::kRows) * tk::kDim);
+  w.take<__nv_bfloat16>((size_t)(N + tk::kTile) * tk::kDim);
+  w.take<float>(Q);
+  w.take<int32_t>(2);
+  w.take<int32_t>(Q);
+  w.take<int32_t>((size_t)nsplit * Q * kc);
+  w.take<float>((size_t)nsplit * Q * kc);
+  w.take<char>(simt_topk_workspace(Q, N, k, true));
+  return align_up(w.off, 1024) + 1024;
+}
+
+int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
+            float* score, int32_t* n_unsafe, void* ws, size_t ws_bytes, cudaStream_t st) {
+  PCLIP_REQUIRE(D == tk::kDim, PCLIP_ERR_UNSUPPORTED, "topk: bf16 tensor-core path needs D == %d (got %d)", tk::kDim, D);
+  PCLIP_REQUIRE(N < (int64_t)0x7fffff00, PCLIP_ERR_UNSUPPORTED, "topk: N must fit 31 bits per call (shard the bank)");
+  PCLIP_REQUIRE((reinterpret_cast<uintptr_t>(q) & 15) == 0 && (reinterpret_cast<uintptr_t>(bank) & 15) == 0,
+                PCLIP_ERR_INVALID, "topk: q and bank must be 16-byte aligned");
+  const int kc = cand_per_query(k);
+  PCLIP_REQUIRE(k <= kc, PCLIP_ERR_UNSUPPORTED, "topk: bf16 path supports k <= %d", tk::kMaxCand);
+  int nsplit, tps;
+  plan_topk_split(Q, N, kc, &nsplit, &tps);
+  PCLIP_REQUIRE(ws && (reinterpret_cast<uintptr_t>(ws) & 1023) == 0, PCLIP_ERR_WORKSPACE,
+                "topk: workspace must be 1024-byte aligned");
+  TopkWs t = carve(ws, ws_bytes, Q, N, k, kc, nsplit);
+  PCLIP_REQUIRE(t.ok, PCLIP_ERR_WORKSPACE, "topk: workspace too small (%zu < %zu)", ws_bytes,
+                tc_topk_workspace(Q, N, k));
+  PCLIP_CHECK_CUDA(cudaMemsetAsync(t.scalars, 0, 2 * sizeof(int32_t), st));
+  const int cblocks = 148 * 8;
+  to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(q, Q, t.qb, t.qnorm, nullptr);
+  PCLIP_CHECK_LAUNCH();
+  to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(bank, N, t.bb, nullptr, t.scalars);
+  PCLIP_CHECK_LAUNCH();
+  CUtensorMap mq, mb;
+  PCLIP_TRY(make_tmap_bf16_2d(&mq, t.qb, (uint64_t)Q, tk::kDim, tk::kDim, tk::kTile, 64));
+  PCLIP_TRY(make_tmap_bf16_2d(&mb, t.bb, (uint64_t)N, tk::kDim, tk::kDim, tk::kTile, 64));
+  TopkArgs a{Q, N, kc, tps, t.cand_idx, t.cand_score};
+  PCLIP_CHECK_CUDA(
+      cudaFuncSetAttribute(tc_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk::kSmemBytes));
+  dim3 grid((unsigned)ceil_div(Q, tk::kRows), (unsigned)nsplit);
+  tc_topk_kernel<<<grid, tk::kThreads, tk::kSmemBytes, st>>>(mq, mb, a);
+  PCLIP_CHECK_LAUNCH();
+  topk_rescore_kernel<<<(unsigned)ceil_div(Q, kRescoreWarps), kRescoreWarps * 32, 0, st>>>(
+      q, bank, t.cand_idx, t.cand_score, t.qnorm, t.scalars, Q, nsplit, kc, k, index_base, idx, score, t.unsafe,
+      t.scalars + 1);
+  PCLIP_CHECK_LAUNCH();
+  // queries whose exactness could not be proven are recomputed by the exact fp32 kernel (device-side count)
+  PCLIP_TRY(simt_topk(q, bank, Q, N, D, k, index_base, idx, score, t.fix, t.fix_bytes, st, t.unsafe, t.scalars + 1));
+  if (n_unsafe)
+    PCLIP_CHECK_CUDA(cudaMemcpyAsync(n_unsafe, t.scalars + 1, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  return PCLIP_OK;
+}
+
+}  // namespace pclip

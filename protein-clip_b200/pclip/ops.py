@@ -251,3 +251,84 @@ class ClipPlan:
         self.finalize(self.Nb)
         rec("grad", 0); self.grad(self.Nb); rec("grad", 1)
         return self.loss, self.dx, self.dy
+
+
+# ---------------------------------------------------------------------------------------------------------
+# (3) scores / rank of the positive / top-k      ref: modules/training_utils.py:157-172, :219-222;
+#                                                      modules/visualizations.py:51-52; topk.py:47-61
+# ---------------------------------------------------------------------------------------------------------
+def _f32c(t):
+    return t.detach().float().contiguous()
+
+
+def scores(q: torch.Tensor, bank: torch.Tensor, op: str = "dot", neg_tau: torch.Tensor | None = None) -> torch.Tensor:
+    """[Q, N] matrix of q . bank_n ("dot"), exp(q . bank_n) ("exp": get_logits) and, with neg_tau, times exp(-tau)
+    (the cosine matrix of visualizations.py:51-52)."""
+    L.require_cuda(q, bank)
+    q, bank = _f32c(q), _f32c(bank)
+    out = torch.empty(q.shape[0], bank.shape[0], dtype=torch.float32, device=q.device)
+    nt = None if neg_tau is None else neg_tau.detach().reshape(1).float().to(q.device)
+    with torch.cuda.device(q.device):
+        L.check(L.lib().pclip_scores(L.ptr(q), L.ptr(bank), q.shape[0], bank.shape[0], q.shape[1],
+                                     L.SCORE_EXP if op == "exp" else L.SCORE_DOT, L.ptr(nt), L.ptr(out),
+                                     L.stream_ptr(q.device)))
+    return out
+
+
+def rank_of_positive(q: torch.Tensor, bank: torch.Tensor, pos: torch.Tensor) -> torch.Tensor:
+    """rank[i] = 1 + #{n : q_i . bank_n > q_i . bank_pos[i]} (strict), int32 [Q]."""
+    L.require_cuda(q, bank, pos)
+    q, bank = _f32c(q), _f32c(bank)
+    pos = pos.to(torch.int64).contiguous()
+    rank = torch.empty(q.shape[0], dtype=torch.int32, device=q.device)
+    with torch.cuda.device(q.device):
+        L.check(L.lib().pclip_rank_of_positive(L.ptr(q), L.ptr(bank), L.ptr(pos), q.shape[0], bank.shape[0], q.shape[1],
+                                               L.ptr(rank), L.stream_ptr(q.device)))
+    return rank
+
+
+class TopkPlan:
+    """Caller-owned outputs and workspace for repeated top-k calls of one shape (no allocation per call)."""
+
+    def __init__(self, Q: int, N: int, D: int, k: int, compute: int, device):
+        self.Q, self.N, self.D, self.k, self.compute, self.dev = Q, N, D, k, compute, torch.device(device)
+        self.idx = torch.empty(Q, k, dtype=torch.int64, device=device)
+        self.score = torch.empty(Q, k, dtype=torch.float32, device=device)
+        self.n_unsafe = torch.zeros(1, dtype=torch.int32, device=device)
+        self.ws_bytes = int(L.lib().pclip_topk_workspace_bytes(Q, N, D, k, compute))
+        self._owner, self.ws = L.workspace(max(self.ws_bytes, 1024), device)
+
+    def run(self, q: torch.Tensor, bank: torch.Tensor, index_base: int = 0):
+        assert q.shape == (self.Q, self.D) and bank.shape == (self.N, self.D)
+        assert q.dtype == torch.float32 and bank.dtype == torch.float32 and q.is_contiguous() and bank.is_contiguous()
+        with torch.cuda.device(self.dev):
+            L.check(L.lib().pclip_topk(L.ptr(q), L.ptr(bank), self.Q, self.N, self.D, self.k, self.compute, index_base,
+                                       L.ptr(self.idx), L.ptr(self.score), L.ptr(self.n_unsafe), self.ws, self.ws_bytes,
+                                       L.stream_ptr(self.dev)))
+        return self.idx, self.score
+
+
+def topk(q: torch.Tensor, bank: torch.Tensor, k: int, compute: int | None = None, index_base: int = 0):
+    """Top-k bank rows per query by dot product: (idx [Q, k] int64, score [Q, k] fp32), descending, ties -> lower
+    index.  BF16 = tensor-core candidate selection + exact fp32 re-scoring (proven exact per query, else recomputed
+    by the fp32 kernel); F32 = exact fp32 scan."""
+    L.require_cuda(q, bank)
+    q, bank = _f32c(q), _f32c(bank)
+    if compute is None:
+        compute = BF16 if q.shape[1] == 128 else F32
+    plan = TopkPlan(q.shape[0], bank.shape[0], q.shape[1], k, compute, q.device)
+    idx, score = plan.run(q, bank, index_base)
+    plan._owner.record_stream(torch.cuda.current_stream(q.device))
+    return idx, score, plan.n_unsafe
+
+
+def topk_merge(idx_lists: torch.Tensor, score_lists: torch.Tensor):
+    """Merge [n_lists, Q, k] per-shard candidates (global indices) into the global top-k (bank-sharded mode)."""
+    L.require_cuda(idx_lists, score_lists)
+    n, Q, k = idx_lists.shape
+    idx = torch.empty(Q, k, dtype=torch.int64, device=idx_lists.device)
+    score = torch.empty(Q, k, dtype=torch.float32, device=idx_lists.device)
+    with torch.cuda.device(idx.device):
+        L.check(L.lib().pclip_topk_merge(L.ptr(idx_lists.contiguous()), L.ptr(score_lists.contiguous()), Q, n, k,
+                                         L.ptr(idx), L.ptr(score), L.stream_ptr(idx.device)))
+    return idx, score
