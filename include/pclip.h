@@ -182,26 +182,32 @@ int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, in
  * (4) FILIP token-wise late interaction.
  *     ref: modules/models.py:292-356 (_filip_similarity_score), :247-264 (_masked_mean)
  *          modules/training_utils_filip.py:4-39 (_contrastive_loss row-wise on BOTH matrices, _compute_loss)
- *     S[a,b,t,s] = <hA[a,t], hB[b,s]> / tau over the valid prefixes lenA[a] x lenB[b];
- *     simA[a,b] = mean_{t valid} max_s S,  simB[a,b] = mean_{s valid} max_t S  (0 when a side is empty).
- *     argA[a,b,t] / argB[a,b,s] record the maximising token (lowest index on exact ties) for backward.
+ *     S[a,b,t,s] = <hA[a,t], hB[b,s]> / tau over the valid prefixes lenA[a] x lenB[b] (right-padded masks);
+ *     simA[a,b] = sum_{t < lenA[a]} max_{s < lenB[b]} S / max(lenA[a], 1e-6)
+ *     simB[a,b] = sum_{s < lenB[b]} max_{t < lenA[a]} S / max(lenB[b], 1e-6)
+ *     argA[a,b,t] / argB[b,a,s] (NOTE the [Bb,Ba,TB] layout of argB) record the maximising token, lowest index
+ *     on exact ties, for the backward pass.  hA / hB are what _filip_similarity_score receives (already
+ *     normalised by the caller, ref: models.py:238-239 -> pclip_normalize_scale_fwd with eps = 0, tau = NULL).
+ *     tau must be > 0 (the reference's nn.Parameter(1.0)); tau <= 0 yields NaN outputs.
+ *     Ba != Bb is allowed: a rank of an A-row-sharded job passes its rows of hA and all of hB.
+ *     compute == BF16 needs D == 128 and TA, TB <= 32767.
  * ---------------------------------------------------------------------------------------------- */
 size_t pclip_filip_workspace_bytes(int64_t Ba, int64_t Bb, int64_t TA, int64_t TB, int32_t D, int32_t compute);
 
 int pclip_filip_fwd(const float* hA /* [Ba,TA,D] */, const float* hB /* [Bb,TB,D] */,
                     const int32_t* lenA /* [Ba] */, const int32_t* lenB /* [Bb] */, int64_t Ba, int64_t Bb,
                     int64_t TA, int64_t TB, int32_t D, const float* tau /* dev [1] */, int32_t compute,
-                    float* simA /* [Ba,Bb] */, float* simB /* [Ba,Bb] */, int16_t* argA /* [Ba,Bb,TA] or NULL */,
-                    int16_t* argB /* [Ba,Bb,TB] or NULL */, void* workspace, size_t workspace_bytes,
+                    float* simA /* [Ba,Bb] */, float* simB /* [Ba,Bb] */, int16_t* argA /* [Ba,Bb,TA] */,
+                    int16_t* argB /* [Bb,Ba,TB] */, void* workspace, size_t workspace_bytes,
                     pclip_stream_t stream);
 
 /* gA / gB: upstream gradients of simA / simB [Ba,Bb].  dhA [Ba,TA,D], dhB [Bb,TB,D] are OVERWRITTEN,
- * dtau [1] is accumulated. */
+ * dtau [1] is accumulated (dtau += -(sum gA simA + sum gB simB) / tau). */
 int pclip_filip_bwd(const float* hA, const float* hB, const int32_t* lenA, const int32_t* lenB, int64_t Ba,
-                    int64_t Bb, int64_t TA, int64_t TB, int32_t D, const float* tau, const float* simA,
-                    const float* simB, const int16_t* argA, const int16_t* argB, const float* gA, const float* gB,
-                    float* dhA, float* dhB, float* dtau, void* workspace, size_t workspace_bytes,
-                    pclip_stream_t stream);
+                    int64_t Bb, int64_t TA, int64_t TB, int32_t D, const float* tau, int32_t compute,
+                    const float* simA, const float* simB, const int16_t* argA, const int16_t* argB,
+                    const float* gA, const float* gB, float* dhA, float* dhB, float* dtau, void* workspace,
+                    size_t workspace_bytes, pclip_stream_t stream);
 
 /* row-wise InfoNCE on a [B, Bc] logits matrix whose positives sit at column diag_offset + i:
  *   loss (+)= scale * sum_i (log sum_j exp L_ij - L_i,diag);  dlogits = scale * (softmax_row - onehot)

@@ -96,6 +96,16 @@ int tc_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale,
 size_t tc_topk_workspace(int64_t Q, int64_t N, int k);
 int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
             float* score, int32_t* n_unsafe, void* ws, size_t ws_bytes, cudaStream_t st);
+// FILIP (filip.cu: fp32 path + tails; filip_tc.cu: bf16 tcgen05 path)
+int filip_finalize(const float* part, int np, const int32_t* lenX, int Bx, int By, int Tx, const float* tau, float* out,
+                   int64_t so0, int64_t so1, cudaStream_t st);
+size_t tc_filip_workspace(int64_t Ba, int64_t Bb, int64_t TA, int64_t TB);
+int tc_filip_fwd(const float* hA, const float* hB, const int32_t* lenA, const int32_t* lenB, int64_t Ba, int64_t Bb,
+                 int64_t TA, int64_t TB, int D, const float* tau, float* simA, float* simB, int16_t* argA,
+                 int16_t* argB, void* ws, size_t ws_bytes, cudaStream_t st);
+int tc_filip_bwd(const float* hA, const float* hB, const int32_t* lenA, const int32_t* lenB, int64_t Ba, int64_t Bb,
+                 int64_t TA, int64_t TB, int D, const float* tau, const int16_t* argA, const int16_t* argB,
+                 const float* gA, const float* gB, float* dhA, float* dhB, void* ws, size_t ws_bytes, cudaStream_t st);
 // exact fp32 top-k on CUDA cores (scores.cu)
 // qlist / qcount (device, optional): "list mode" -- only queries qlist[0 .. *qcount) are recomputed, in place
 size_t simt_topk_workspace(int64_t Q, int64_t N, int k, bool list_mode);

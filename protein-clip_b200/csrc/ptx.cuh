@@ -95,14 +95,14 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 
 // Blocking wait with a watchdog: a pipeline bug must trap, never hang the device.
 #ifndef PCLIP_MBAR_TIMEOUT_NS
-#define PCLIP_MBAR_TIMEOUT_NS 4000000000ull
+#define PCLIP_MBAR_TIMEOUT_NS 2000000000ull
 #endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const uint64_t t0 = global_timer_ns();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0x3ff) == 0 && global_timer_ns() - t0 > PCLIP_MBAR_TIMEOUT_NS) {
+    if ((++spins & 0x7) == 0 && global_timer_ns() - t0 > PCLIP_MBAR_TIMEOUT_NS) {
       printf("pclip: mbarrier timeout block=(%d,%d) thread=%d bar=%u parity=%u\n", blockIdx.x, blockIdx.y,
              threadIdx.x, smem_u32(bar), parity);
       __trap();

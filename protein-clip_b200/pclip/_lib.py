@@ -66,8 +66,8 @@ SIGNATURES = {
     "pclip_topk_merge": (C.c_int, [_P, _P, _I64, _I32, _I32, _P, _P, _P]),
     "pclip_filip_workspace_bytes": (_SZ, [_I64, _I64, _I64, _I64, _I32, _I32]),
     "pclip_filip_fwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _I32, _P, _P, _P, _P, _P, _SZ, _P]),
-    "pclip_filip_bwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
-                                  _P, _SZ, _P]),
+    "pclip_filip_bwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P,
+                                  _P, _P, _SZ, _P]),
     "pclip_rowwise_infonce": (C.c_int, [_P, _I64, _I64, _I64, _F, _P, _P, _P]),
 }
 

@@ -332,3 +332,114 @@ def topk_merge(idx_lists: torch.Tensor, score_lists: torch.Tensor):
         L.check(L.lib().pclip_topk_merge(L.ptr(idx_lists.contiguous()), L.ptr(score_lists.contiguous()), Q, n, k,
                                          L.ptr(idx), L.ptr(score), L.stream_ptr(idx.device)))
     return idx, score
+
+
+# ---------------------------------------------------------------------------------------------------------
+# (4) FILIP token-wise late interaction    ref: modules/models.py:292-356; modules/training_utils_filip.py:4-39
+# ---------------------------------------------------------------------------------------------------------
+def mask_lengths(mask: torch.Tensor) -> torch.Tensor:
+    """Right-padded attention mask [B, T] (a contiguous prefix of ones, as the ESM tokenizer produces with
+    padding=True, ref: modules/training_utils_filip.py:56-57) -> int32 lengths.  Set PCLIP_CHECK_MASKS=1 to verify the
+    prefix property (costs a host sync)."""
+    m = mask.to(torch.bool)
+    lens = m.sum(dim=1).to(torch.int32)
+    if os.environ.get("PCLIP_CHECK_MASKS") == "1":
+        T = m.shape[1]
+        want = torch.arange(T, device=m.device)[None, :] < lens[:, None]
+        if not bool((want == m).all()):
+            raise L.PclipError("FILIP kernels need right-padded masks (a prefix of ones per row)")
+    return lens.contiguous()
+
+
+class _FilipSimilarity(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, hA, hB, lenA, lenB, tau, compute):
+        L.require_cuda(hA, hB, lenA, lenB)
+        dev = hA.device
+        a, b = hA.detach().float().contiguous(), hB.detach().float().contiguous()
+        Ba, TA, D = a.shape
+        Bb, TB, _ = b.shape
+        tau_d = tau.detach().reshape(1).float().to(dev)
+        lib = L.lib()
+        nbytes = int(lib.pclip_filip_workspace_bytes(Ba, Bb, TA, TB, D, compute))
+        owner, ws = L.workspace(nbytes, dev)
+        simA = torch.empty(Ba, Bb, dtype=torch.float32, device=dev)
+        simB = torch.empty(Ba, Bb, dtype=torch.float32, device=dev)
+        argA = torch.empty(Ba, Bb, TA, dtype=torch.int16, device=dev)
+        argB = torch.empty(Bb, Ba, TB, dtype=torch.int16, device=dev)
+        with torch.cuda.device(dev):
+            L.check(lib.pclip_filip_fwd(L.ptr(a), L.ptr(b), L.ptr(lenA), L.ptr(lenB), Ba, Bb, TA, TB, D, L.ptr(tau_d),
+                                        compute, L.ptr(simA), L.ptr(simB), L.ptr(argA), L.ptr(argB), ws, nbytes,
+                                        L.stream_ptr(dev)))
+        owner.record_stream(torch.cuda.current_stream(dev))
+        ctx.save_for_backward(a, b, lenA, lenB, tau_d, simA, simB, argA, argB)
+        ctx.compute = compute
+        ctx.tau_shape = tau.shape
+        ctx.in_dtypes = (hA.dtype, hB.dtype)
+        return simA, simB
+
+    @staticmethod
+    def backward(ctx, gA, gB):
+        a, b, lenA, lenB, tau_d, simA, simB, argA, argB = ctx.saved_tensors
+        dev = a.device
+        Ba, TA, D = a.shape
+        Bb, TB, _ = b.shape
+        gA = torch.zeros_like(simA) if gA is None else gA.float().contiguous()
+        gB = torch.zeros_like(simB) if gB is None else gB.float().contiguous()
+        lib = L.lib()
+        nbytes = int(lib.pclip_filip_workspace_bytes(Ba, Bb, TA, TB, D, ctx.compute))
+        owner, ws = L.workspace(nbytes, dev)
+        dhA, dhB = torch.empty_like(a), torch.empty_like(b)
+        dtau = torch.zeros(1, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            L.check(lib.pclip_filip_bwd(L.ptr(a), L.ptr(b), L.ptr(lenA), L.ptr(lenB), Ba, Bb, TA, TB, D, L.ptr(tau_d),
+                                        ctx.compute, L.ptr(simA), L.ptr(simB), L.ptr(argA), L.ptr(argB), L.ptr(gA),
+                                        L.ptr(gB), L.ptr(dhA), L.ptr(dhB), L.ptr(dtau), ws, nbytes, L.stream_ptr(dev)))
+        owner.record_stream(torch.cuda.current_stream(dev))
+        return (dhA.to(ctx.in_dtypes[0]), dhB.to(ctx.in_dtypes[1]), None, None, dtau.reshape(ctx.tau_shape), None)
+
+
+def filip_similarity(hA, hB, maskA, maskB, tau, compute: int | None = None):
+    """(simA, simB) [Ba, Bb] of ExtendedFILIP._filip_similarity_score for right-padded masks (or int32 lengths)."""
+    if compute is None:
+        compute = default_compute()
+    lenA = maskA if maskA.dim() == 1 else mask_lengths(maskA)
+    lenB = maskB if maskB.dim() == 1 else mask_lengths(maskB)
+    tau = torch.as_tensor(tau, device=hA.device)
+    return _FilipSimilarity.apply(hA, hB, lenA.to(torch.int32), lenB.to(torch.int32), tau, compute)
+
+
+class _RowwiseInfoNCE(torch.autograd.Function):
+    """mean_i(-L_ii + log sum_j exp L_ij) * weight  (ref: modules/training_utils_filip.py:15-23, use_dcl=False)."""
+
+    @staticmethod
+    def forward(ctx, logits, weight, diag_offset):
+        L.require_cuda(logits)
+        lg = logits.detach().float().contiguous()
+        B, Bc = lg.shape
+        loss = torch.zeros(1, dtype=torch.float32, device=lg.device)
+        dl = torch.empty_like(lg) if logits.requires_grad else None
+        with torch.cuda.device(lg.device):
+            L.check(L.lib().pclip_rowwise_infonce(L.ptr(lg), B, Bc, diag_offset, float(weight) / B, L.ptr(loss), L.ptr(dl),
+                                                  L.stream_ptr(lg.device)))
+        if dl is not None:
+            ctx.save_for_backward(dl)
+        ctx.in_dtype = logits.dtype
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        g = g.reshape(1).float().contiguous()
+        out = torch.empty_like(dl)
+        L.check(L.lib().pclip_scale_by_scalar(L.ptr(dl), L.ptr(g), dl.numel(), L.ptr(out), L.stream_ptr(dl.device)))
+        return out.to(ctx.in_dtype), None, None
+
+
+def rowwise_infonce(logits: torch.Tensor, weight: float = 1.0, diag_offset: int = 0) -> torch.Tensor:
+    return _RowwiseInfoNCE.apply(logits, weight, diag_offset)
+
+
+def filip_loss(simA: torch.Tensor, simB: torch.Tensor, diag_offset: int = 0) -> torch.Tensor:
+    """(loss_A + loss_B) / 2 with BOTH matrices normalised row-wise (ref: training_utils_filip.py:26-39)."""
+    return rowwise_infonce(simA, 0.5, diag_offset) + rowwise_infonce(simB, 0.5, diag_offset)
