@@ -263,6 +263,66 @@ class ClipGradCache:
                 "note": "launch-latency bound (50 MFLOP): roofline fraction not meaningful; includes autograd overhead"}
 
 
+class FilipB256:
+    """configs[2]: FILIP token-wise late interaction fwd+bwd (normalise -> similarity -> row-wise InfoNCE -> backward),
+    B = 256, T = 512/512 (ref: modules/models.py:238-239, :292-356; training_utils_filip.py:26-39), bf16 tensor cores."""
+    name = "filip_b256"
+
+    def __init__(self, dist: Dist, B=256, T=512, ragged=False):
+        from pclip import ops, synth
+        self.ops, self.B, self.T, self.ragged = ops, B, T, ragged
+        hA, hB, mA, mB, tau = synth.filip_tokens(B, T, T, cfg_id=3, ragged=ragged)
+        self.hA, self.hB = hA.to(dist.dev).requires_grad_(), hB.to(dist.dev).requires_grad_()
+        self.lenA = mA.sum(1).to(torch.int32).to(dist.dev)
+        self.lenB = mB.sum(1).to(torch.int32).to(dist.dev)
+        self.tau = tau.to(dist.dev).requires_grad_()
+        self.pair_tokens = float((mA.sum(1).double()[:, None] * mB.sum(1).double()[None, :]).sum())
+
+    def step(self):
+        ops = self.ops
+        self.hA.grad = self.hB.grad = self.tau.grad = None
+        nA = ops.normalize_scale(self.hA, None, eps=0.0)
+        nB = ops.normalize_scale(self.hB, None, eps=0.0)
+        simA, simB = ops.filip_similarity(nA, nB, self.lenA, self.lenB, self.tau, compute=ops.BF16)
+        ops.filip_loss(simA, simB).backward()
+
+    def report(self, dist, peaks, steps=5, warmup=2):
+        self.ops.reset_launch_count()
+        ms = timed(dist, self.step, steps, warmup) / steps
+        flops = 2.0 * self.pair_tokens * 128              # the token-similarity contraction (algorithmic, once)
+        return {"ms_per_step": round(ms, 3), "pairs_per_s": round(self.B / (ms * 1e-3), 1),
+                "lengths": "PDB-like ragged" if self.ragged else "all 512",
+                "algorithmic_tflops": round(flops / (ms * 1e-3) / 1e12, 1),
+                "frac_of_tensor_peak": round(flops / (ms * 1e-3) / 1e12 / peaks["tc"], 4),
+                "pclip_launches_per_step": self.ops.launch_count() / (steps + warmup)}
+
+
+class Topk4M:
+    """configs[4]: top-10 by cosine over a 2^22-row bank (ref: rank / top-k of training_utils.py:219-222, topk.py:47-61),
+    bf16 tensor-core candidate selection + exact fp32 re-scoring; queries stream through in batches of Q."""
+    name = "topk_4m"
+
+    def __init__(self, dist: Dist, N=1 << 22, Q=1 << 18, k=10):
+        from pclip import ops, synth
+        self.ops, self.N, self.Q, self.k = ops, N, Q, k
+        self.bank, self.q, self.pos = synth.retrieval_bank(N, Q, cfg_id=5, device=dist.dev)
+        self.plan = ops.TopkPlan(Q, N, 128, k, ops.BF16, dist.dev)
+
+    def step(self):
+        self.plan.run(self.q, self.bank)
+
+    def report(self, dist, peaks, steps=3, warmup=1):
+        self.ops.reset_launch_count()
+        ms = timed(dist, self.step, steps, warmup) / steps
+        flops = 2.0 * self.Q * self.N * 128
+        recall = float((self.plan.idx[:, 0] == self.pos).float().mean())
+        return {"ms_per_step": round(ms, 3), "queries_per_s": round(self.Q / (ms * 1e-3), 1), "Q_per_step": self.Q,
+                "N": self.N, "k": self.k, "algorithmic_tflops": round(flops / (ms * 1e-3) / 1e12, 1),
+                "frac_of_tensor_peak": round(flops / (ms * 1e-3) / 1e12 / peaks["tc"], 4),
+                "unproven_queries": int(self.plan.n_unsafe), "top1_is_planted_positive": round(recall, 4),
+                "pclip_launches_per_step": self.ops.launch_count() / (steps + warmup)}
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU arithmetic for the path (oracle port: the reference is Python and
     cannot travel to the GPU box) on all host cores, each step a bounded sample of the same workload."""
@@ -338,7 +398,18 @@ def main():
         "step_frac_of_tensor_peak": round(6.0 * w.B * w.B * w.D / (ms / args.steps * 1e-3) / 1e12 / peaks["tc"], 4),
     }
     if dist.rank == 0 and dist.world == 1 and not args.no_extras:
-        out["workloads"] = {"clip_gc256": ClipGradCache(dist).report(dist)}
+        del w.plan, w.job
+        extras = {"clip_gc256": ClipGradCache(dist).report(dist)}
+        for name, make in (("filip_b256", lambda: FilipB256(dist)), ("filip_b256_ragged", lambda: FilipB256(dist, ragged=True)),
+                           ("topk_4m", lambda: Topk4M(dist))):
+            try:
+                wl = make()
+                extras[name] = wl.report(dist, peaks)
+                del wl
+            except Exception as e:  # a secondary workload must not take the headline line down
+                extras[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+            torch.cuda.empty_cache()
+        out["workloads"] = extras
         out["cpu_baseline"] = w.cpu_sample()
     elif dist.rank == 0:
         out["cpu_baseline"] = None
