@@ -1,0 +1,148 @@
+"""GPU tests of the drop-in `modules` package: the entry scripts' call sequence (tokenise -> model -> loss -> backward,
+GradCache accumulate / replay, rank evaluation) on a random 2-layer ESM, checked against the oracle's restatement of the
+reference arithmetic applied to the SAME encoder outputs."""
+import copy
+import os
+import sys
+
+import pytest
+import torch
+
+from oracle import restate as R
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import _tiny  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def _oracle_encoder(enc, seq, tau):
+    """Trunk in stock torch + the oracle's tail (differentiable): what the reference's Encoder.forward computes."""
+    h = enc.esm_model(input_ids=seq["input_ids"], attention_mask=seq["attention_mask"]).last_hidden_state
+    pooled = enc._masked_mean(enc.amino_acid_ffn(enc.projection(h)), seq["attention_mask"])
+    return R.normalize_scale(enc.embedding_ffn(pooled), tau)
+
+
+@pytest.fixture()
+def clip_model():
+    from modules import models
+    torch.manual_seed(1)
+    return models.ExtendedCLIP(40, 128, 2, 2, 0.0, _tiny.tiny_esm()).to(DEV)
+
+
+def test_clip_process_batch_matches_oracle(clip_model):
+    from modules import training_utils as tu
+    tok = _tiny.TinyTokenizer()
+    batch = _tiny.loader(1, 16, seed=3)[0]
+    model = clip_model
+    ref = copy.deepcopy(model)
+    model.train()
+    loss = tu._process_batch(model, batch, tok, DEV, compute_grad=True)
+    pep, rec = tok(batch[0]).to(DEV), tok(batch[1]).to(DEV)
+    lo = R.clip_loss(_oracle_encoder(ref.pep_encoder, pep, ref.temperature),
+                     _oracle_encoder(ref.rec_encoder, rec, ref.temperature).t())
+    lo.backward()
+    assert abs(loss - float(lo)) <= 1e-5 * abs(float(lo))
+    for (n, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
+        if q.grad is not None:
+            assert p.grad is not None and rel(p.grad, q.grad) <= 2e-4, n
+    # evaluate(): same value without grad, dict mutation side effect of forward
+    seq_p, seq_r = tok(batch[0]).to(DEV), tok(batch[1]).to(DEV)
+    model.eval()
+    with torch.no_grad():
+        model(seq_p, seq_r)
+    assert seq_p["temperature"] is model.temperature and seq_r["temperature"] is model.temperature
+    assert abs(tu.evaluate(model, [batch], tok, DEV) - float(lo)) <= 1e-5 * abs(float(lo))
+
+
+def test_train_gc_matches_uncached_big_batch(clip_model):
+    """4 sub-batches x 8 pairs accumulated with GradCache + GradScaler == one 32-pair batch (ref: train_gc :92-155)."""
+    from modules import training_utils as tu
+    tok = _tiny.TinyTokenizer()
+    data = _tiny.loader(4, 8, seed=5)
+    model = clip_model
+    ref = copy.deepcopy(model)
+    opt = torch.optim.SGD([p for p in model.parameters() if p.requires_grad], lr=0.0)   # lr 0: keep grads inspectable
+    scaler = torch.amp.GradScaler("cuda", init_scale=65536.0)
+    grads = {}
+    orig_step = scaler.step
+
+    def spy(optimizer):      # grads are zeroed at the end of train_gc's group; capture them (still scaled) here
+        for n, p in model.named_parameters():
+            if p.grad is not None:
+                grads[n] = p.grad.detach().clone() / 65536.0
+        return orig_step(optimizer)
+
+    scaler.step = spy
+    loss = tu.train_gc(model, data, tok, opt, scaler, DEV, accumulated_batches=4)
+    reps_x = [_oracle_encoder(ref.pep_encoder, tok(b[0]).to(DEV), ref.temperature) for b in data]
+    reps_y = [_oracle_encoder(ref.rec_encoder, tok(b[1]).to(DEV), ref.temperature) for b in data]
+    lo = R.clip_loss_gc(reps_x, reps_y)
+    lo.backward()
+    assert abs(loss - float(lo)) <= 1e-2 * abs(float(lo))      # bf16 tensor-core contraction (reference: fp16 autocast)
+    assert grads, "no parameter gradients reached the optimizer"
+    for n, q in ref.named_parameters():
+        if q.grad is not None and q.grad.abs().max() > 0:
+            # fp16-autocast trunk replay + bf16 loss contraction against an all-fp32 restatement
+            fro = float((grads[n].double() - q.grad.double()).norm() / q.grad.double().norm())
+            assert n in grads and fro <= 3e-2 and rel(grads[n], q.grad) <= 1e-1, (n, fro, rel(grads[n], q.grad))
+
+
+def test_rank_evaluation_and_cosine_matrix(clip_model):
+    from modules import training_utils as tu, visualizations as vis
+    tok = _tiny.TinyTokenizer()
+    data = _tiny.loader(4, 8, seed=9)
+    model = clip_model.eval()
+    with torch.no_grad():
+        reps_y = torch.cat([_oracle_encoder(model.rec_encoder, tok(b[1]).to(DEV), model.temperature) for b in data])
+        for k in (0, 5, 17, 31):
+            qs = data[k // 8][0][k % 8]
+            q = _oracle_encoder(model.pep_encoder, tok((qs,)).to(DEV), model.temperature)
+            want = R.rank_of_positive((q @ reps_y.t()).exp()[0].cpu(), k)
+            assert tu.eval_gc_allrec_onepep(model, data, DEV, tok, agg_batches=4, k=k) == [want]
+        pep, rec = tok(data[0][0]).to(DEV), tok(data[0][1]).to(DEV)
+        cos = vis._compute_embedding_cosine_similarities(model, pep, rec)
+        p, r = model(tok(data[0][0]).to(DEV), tok(data[0][1]).to(DEV))
+        assert rel(cos, R.cosine_matrix(p, r, model.temperature.detach())) <= 1e-5
+        assert float(cos.abs().max()) <= 1.0 + 1e-5
+        lg = tu.get_logits([p[:4], p[4:]], [r[:3], r[3:]])
+        assert rel(lg, R.get_logits(p, r)) <= 1e-5
+
+
+def test_filip_process_batch_matches_oracle():
+    from modules import models, training_utils_filip as tf
+    torch.manual_seed(2)
+    model = models.ExtendedFILIP(40, 128, 2, 2, 0.0, _tiny.tiny_esm()).to(DEV)
+    ref = copy.deepcopy(model)
+    tok = _tiny.TinyTokenizer()
+    batch = _tiny.loader(1, 6, seed=13)[0]
+    model.train()
+    loss = tf._process_batch(model, batch, tok, DEV, compute_grad=True)
+    pep, rec = tok(batch[0]).to(DEV), tok(batch[1]).to(DEV)
+    hA, mA = ref.pep_encoder({**pep, "temperature": ref.temperature})
+    hB, mB = ref.rec_encoder({**rec, "temperature": ref.temperature})
+    simA, simB = R.filip_similarity(R.filip_normalize(hA).cpu(), R.filip_normalize(hB).cpu(), mA.cpu(), mB.cpu(),
+                                    ref.temperature.detach().cpu())
+    lo_val = R.filip_compute_loss(simA, simB)
+    assert abs(loss - float(lo_val)) <= 1e-5 * abs(float(lo_val))
+    # gradients: autograd through the literal torch restatement on the device
+    nA, nB = R.filip_normalize(hA), R.filip_normalize(hB)
+    s = torch.einsum("atd,bsd->abts", nA, nB) / ref.temperature
+    valid = mA.bool()[:, None, :, None] & mB.bool()[None, :, None, :]
+    s = s.masked_fill(~valid, torch.finfo(s.dtype).min)
+    rA = R.masked_mean(s.amax(dim=3), mA.bool()[:, None, :].expand(-1, s.shape[1], -1), dim=-1)
+    rB = R.masked_mean(s.amax(dim=2), mB.bool()[None, :, :].expand(s.shape[0], -1, -1), dim=-1)
+    lo = R.filip_compute_loss(rA, rB)
+    lo.backward()
+    for (n, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
+        if q.grad is not None and q.grad.abs().max() > 0:
+            assert p.grad is not None and rel(p.grad, q.grad) <= 5e-4, (n, rel(p.grad, q.grad))
+    assert abs(tf.evaluate(model, [batch], tok, DEV) - float(lo_val)) <= 1e-5 * abs(float(lo_val))
+    assert float(tf._contrastive_loss(rA.detach(), use_dcl=True)) == pytest.approx(
+        float(R.filip_contrastive_loss(rA.detach().cpu(), use_dcl=True)), rel=1e-5)
