@@ -1,4 +1,5 @@
 // libpclip.so: error plumbing, launch bookkeeping and the composite CLIP entry points (include/pclip.h).
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -32,6 +33,15 @@ int device_sm_count() {
   return cached_sms;
 }
 
+int clip_generation() {
+  static int gen = 0;
+  if (!gen) {
+    const char* e = getenv("PCLIP_CLIP_GEN");
+    gen = (e && e[0] == '1') ? 1 : 2;
+  }
+  return gen;
+}
+
 int require_device() {
   int n = 0;
   cudaError_t e = cudaGetDeviceCount(&n);
@@ -61,7 +71,8 @@ size_t pclip_clip_rowsumexp_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, i
 
 size_t pclip_clip_grad_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, int32_t compute) {
   (void)D;
-  return compute == PCLIP_COMPUTE_BF16 ? tc_grad_workspace(Ma, Nb) : 0;
+  if (compute != PCLIP_COMPUTE_BF16) return 0;
+  return std::max(tc_grad_workspace(Ma, Nb), tc2_grad_workspace(Ma, Nb));
 }
 
 static size_t ld_transposed(int64_t rows) { return align_up((size_t)rows, 64); }
@@ -94,7 +105,9 @@ int pclip_clip_grad(const pclip_clip_bwd_side_t* sides, int32_t n_sides, int32_t
   PCLIP_TRY(require_device());
   PCLIP_REQUIRE(sides && n_sides >= 1 && n_sides <= 2, PCLIP_ERR_INVALID, "grad: n_sides must be 1 or 2");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (compute == PCLIP_COMPUTE_BF16) return tc_grad(sides, n_sides, D, scale, gscale, workspace, workspace_bytes, st);
+  if (compute == PCLIP_COMPUTE_BF16)
+    return clip_generation() == 1 ? tc_grad(sides, n_sides, D, scale, gscale, workspace, workspace_bytes, st)
+                                  : tc2_grad(sides, n_sides, D, scale, gscale, workspace, workspace_bytes, st);
   if (compute == PCLIP_COMPUTE_F32) return simt_grad(sides, n_sides, D, scale, gscale, st);
   return fail(PCLIP_ERR_UNSUPPORTED, "grad: unknown compute mode %d", compute);
 }

@@ -1,0 +1,700 @@
+// Second-generation BF16 tensor-core kernels of the CLIP InfoNCE contractions (PCLIP_COMPUTE_BF16, D == 128).
+//   ref: modules/training_utils.py:85-89 (S = x @ y.T; exp; row / column sums; loss) and its autograd backward.
+//
+// Differences from clip_tc.cu (first generation, kept for A/B runs through PCLIP_CLIP_GEN=1):
+//   * 256-row CTAs: two 128-row UMMA tiles share every streamed column tile (half the L2 -> SMEM operand traffic).
+//   * the column tile is loaded ONCE: the second MMA of the gradient (P . Y) reads the same shared-memory tile as an
+//     MN-major B operand, so no transposed copy of the embeddings exists in HBM any more.
+//   * 8 epilogue warps (two per SM sub-partition), tcgen05.ld software-pipelined one 32-column chunk ahead.
+//   * exp2 is split between the MUFU (ex2.approx) and a Cody-Waite + minimax polynomial on the FMA pipes (packed
+//     f32x2 FFMA2), because at D = 128 the MUFU rate (16 / clk / SM) -- not the tensor core -- bounds a score tile.
+//   * tc2_sumexp_kernel is single-pass: row sums in-thread, column sums by a third, M = 64 "ones" MMA over the bf16
+//     exp tile (the tile is the MN-major B operand), instead of recomputing the transposed score matrix.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace pclip {
+namespace c2 {
+
+constexpr int kTile = 128;
+constexpr int kDim = 128;
+constexpr uint32_t kPanelBytes = 128 * 128;
+constexpr uint32_t kTileBytes = 2 * kPanelBytes;
+constexpr int kH = 2;
+constexpr int kRows = kH * kTile;
+constexpr int kThreads = 64 + 32 * 4 * kH;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kMagic = 12582912.0f;  // 1.5 * 2^23: (x + kMagic) holds round(x) in its low mantissa bits
+
+// K-major operand ([rows][64 bf16] panels): k-step k covers 16 bf16 = 32 B inside a 128 B swizzled row.
+__device__ __forceinline__ uint64_t kmajor_desc(uint32_t tile_addr, int k) {
+  return make_smem_desc_sw128(tile_addr + (uint32_t)(k >> 2) * kPanelBytes + (uint32_t)(k & 3) * 32u, 16, 1024);
+}
+// The same tile read as an MN-major operand (MN runs along the 128 B rows, K along the tile's rows): k-step k covers
+// tile rows [16k, 16k+16) = two 8-row swizzle atoms (SBO = 1024 B); the two 64-element MN halves are the two panels
+// (LBO = kPanelBytes).
+__device__ __forceinline__ uint64_t mnmajor_desc(uint32_t tile_addr, int k) {
+  return make_smem_desc_sw128(tile_addr + (uint32_t)k * 2048u, kPanelBytes, 1024);
+}
+
+// ---- packed f32x2 helpers (FFMA2 / FADD2 / FMUL2 on sm_100) ----
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+// exp(x) for a pair on the FMA pipes: y = x log2(e) = n + f, |f| <= 1/2; 2^f by a minimax polynomial (relative error
+// 7.5e-5 at degree 3, 2.6e-6 at degree 4), 2^n by adding n to the exponent field.  |y| must stay below 126.
+template <int kDegree>
+__device__ __forceinline__ void exp_poly2(float x0, float x1, float& e0, float& e1) {
+  const uint64_t x = pack2(x0, x1);
+  const uint64_t l2 = pack2(kLog2e, kLog2e);
+  const uint64_t t = fma2(x, l2, pack2(kMagic, kMagic));
+  const uint64_t n = add2(t, pack2(-kMagic, -kMagic));
+  const uint64_t f = fma2(x, l2, mul2(n, pack2(-1.0f, -1.0f)));
+  uint64_t p;
+  if (kDegree == 3) {
+    p = fma2(f, pack2(0.055171459913253784f, 0.055171459913253784f), pack2(0.2426108568906784f, 0.2426108568906784f));
+    p = fma2(p, f, pack2(0.6932609677314758f, 0.6932609677314758f));
+    p = fma2(p, f, pack2(0.9999281167984009f, 0.9999281167984009f));
+  } else {
+    p = fma2(f, pack2(0.009570082649588585f, 0.009570082649588585f), pack2(0.05591784417629242f, 0.05591784417629242f));
+    p = fma2(p, f, pack2(0.240247443318367f, 0.240247443318367f));
+    p = fma2(p, f, pack2(0.6931217908859253f, 0.6931217908859253f));
+    p = fma2(p, f, pack2(0.9999992847442627f, 0.9999992847442627f));
+  }
+  float p0, p1, t0, t1;
+  unpack2(p, p0, p1);
+  unpack2(t, t0, t1);
+  e0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+  e1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
+}
+
+__device__ __forceinline__ uint32_t bf16x2_bits(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);  // .x (low half) = lo = the lower column
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+}  // namespace c2
+
+// =================================================================================================================
+// gradient: da_i = scale * ( sum_j exp(a_i . b_j) (rinv_i + cinv_j) b_j  -  2 b_(off + i) )
+// =================================================================================================================
+struct Tc2BwdSide {
+  int64_t Ma, Nb, diag_offset;
+  const float* rinv;
+  const float* cinv;
+  const __nv_bfloat16* b;
+  float* out;  // direct: da [Ma,128]; split: partial [nsplit][Ma][128]
+};
+struct Tc2BwdArgs {
+  Tc2BwdSide s[2];
+  int tiles_per_split;
+  int direct;
+  float scale;
+  const float* gscale;
+};
+
+namespace c2 {
+constexpr int kBwdStages = 3;
+// A (2 tiles) | Y ring | P (2 tiles) | cinv staging [2][128] | barriers
+constexpr uint32_t kBwdSmem = kTileBytes * (kH + kBwdStages + kH) + 2 * kTile * 4 + 256 + 1024;
+static_assert(kBwdSmem <= 232448, "shared memory budget");
+constexpr int kPolyPerChunk = 8;  // of every 32 exps, this many go to the FMA pipes (multiple of 2)
+}  // namespace c2
+
+__global__ void __launch_bounds__(c2::kThreads, 1)
+tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__ CUtensorMap tb0,
+                const __grid_constant__ CUtensorMap ta1, const __grid_constant__ CUtensorMap tb1,
+                const Tc2BwdArgs args) {
+  using namespace c2;
+  const Tc2BwdSide& sd = args.s[blockIdx.z];
+  const CUtensorMap* ta = blockIdx.z == 0 ? &ta0 : &ta1;
+  const CUtensorMap* tb = blockIdx.z == 0 ? &tb0 : &tb1;
+  const int64_t row0 = (int64_t)blockIdx.x * kRows;
+  if (row0 >= sd.Ma) return;
+  const int nh = row0 + kTile < sd.Ma ? 2 : 1;
+  const int ntiles_all = (int)((sd.Nb + kTile - 1) / kTile);
+  const int tile_begin = blockIdx.y * args.tiles_per_split;
+  const int ntiles = max(min(tile_begin + args.tiles_per_split, ntiles_all) - tile_begin, 0);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_tiles = smem;
+  uint8_t* y_tiles = a_tiles + kH * kTileBytes;
+  uint8_t* p_tiles = y_tiles + kBwdStages * kTileBytes;
+  // [2][128], indexed by tile parity.  Both row-tile groups write the SAME values for a tile; the MMA issue order
+  // keeps the groups within one tile of each other, so a slot is never rewritten while the other group reads it.
+  float* cinv_s = reinterpret_cast<float*>(p_tiles + kH * kTileBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(cinv_s + 2 * kTile);
+  uint64_t* a_full = bars;                    // 1
+  uint64_t* y_full = a_full + 1;              // kBwdStages
+  uint64_t* y_empty = y_full + kBwdStages;    // kBwdStages
+  uint64_t* s_full = y_empty + kBwdStages;    // [kH]
+  uint64_t* p_full = s_full + kH;             // [kH]
+  uint64_t* d_full = p_full + kH;             // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(a_full, 1);
+    for (int i = 0; i < kBwdStages; ++i) {
+      mbar_init(&y_full[i], 1);
+      mbar_init(&y_empty[i], 1);
+    }
+    for (int i = 0; i < kH; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 128);
+    }
+    mbar_init(d_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;   // columns [0,256): S of row tile 0 / 1; [256,512): dA of row tile 0 / 1
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(ta);
+      tma_prefetch_desc(tb);
+      mbar_arrive_expect_tx(a_full, (uint32_t)nh * kTileBytes);
+      for (int h = 0; h < nh; ++h) {
+        tma_load_2d(a_tiles + h * kTileBytes, ta, a_full, 0, (int32_t)(row0 + h * kTile));
+        tma_load_2d(a_tiles + h * kTileBytes + kPanelBytes, ta, a_full, 64, (int32_t)(row0 + h * kTile));
+      }
+      for (int t = 0; t < ntiles; ++t) {
+        const int stage = t % kBwdStages;
+        const uint32_t phase = (uint32_t)(t / kBwdStages) & 1u;
+        mbar_wait(&y_empty[stage], phase ^ 1u);
+        mbar_arrive_expect_tx(&y_full[stage], kTileBytes);
+        const int32_t col0 = (tile_begin + t) * kTile;
+        uint8_t* dst = y_tiles + (size_t)stage * kTileBytes;
+        tma_load_2d(dst, tb, &y_full[stage], 0, col0);
+        tma_load_2d(dst + kPanelBytes, tb, &y_full[stage], 64, col0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && ntiles > 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, 0, 0);   // S = A . Y^T   (both K-major)
+      constexpr uint32_t idesc_g = make_idesc_bf16(kTile, kTile, 0, 1);   // dA += P . Y   (Y tile as MN-major B)
+      mbar_wait(a_full, 0);
+      auto issue_s = [&](int h, int t) {
+        const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kBwdStages) * kTileBytes);
+        const uint32_t a_addr = smem_u32(a_tiles + h * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_bf16_ss(tmem_base + (uint32_t)h * kTile, kmajor_desc(a_addr, k), kmajor_desc(y_addr, k), idesc_s,
+                       k > 0 ? 1u : 0u);
+        umma_commit(&s_full[h]);
+      };
+      mbar_wait(&y_full[0], 0);
+      tc_fence_after_sync();
+      for (int h = 0; h < nh; ++h) issue_s(h, 0);
+      for (int t = 0; t < ntiles; ++t) {
+        const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kBwdStages) * kTileBytes);
+        for (int h = 0; h < nh; ++h) {
+          mbar_wait(&p_full[h], (uint32_t)t & 1u);        // P_h(t) written => S_h(t) fully consumed
+          tc_fence_after_sync();
+          const uint32_t p_addr = smem_u32(p_tiles + h * kTileBytes);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_bf16_ss(tmem_base + (uint32_t)(kH + h) * kTile, kmajor_desc(p_addr, k), mnmajor_desc(y_addr, k), idesc_g,
+                         (t > 0 || k > 0) ? 1u : 0u);
+          if (t + 1 < ntiles) {
+            if (h == 0) {
+              const int st = (t + 1) % kBwdStages;
+              mbar_wait(&y_full[st], (uint32_t)((t + 1) / kBwdStages) & 1u);
+              tc_fence_after_sync();
+            }
+            issue_s(h, t + 1);
+          }
+        }
+        umma_commit(&y_empty[t % kBwdStages]);
+      }
+      umma_commit(d_full);
+    }
+  } else {
+    const int h = (warp - 2) >> 2, q = warp & 3;
+    const int i = q * 32 + lane;                       // row inside the tile
+    const int64_t row = row0 + h * kTile + i;
+    const bool live = h < nh;
+    if (live) {
+      const float rinv = row < sd.Ma ? sd.rinv[row] : 0.f;
+      const uint64_t rinv2 = pack2(rinv, rinv);
+      uint8_t* P = p_tiles + h * kTileBytes;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)h * kTile;
+      for (int t = 0; t < ntiles; ++t) {
+        const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
+        float* cs = cinv_s + (t & 1) * kTile;
+        cs[i] = (col0 + i < sd.Nb) ? sd.cinv[col0 + i] : 0.f;   // 0 also masks the zero-filled columns beyond Nb
+        named_bar_sync(1 + h, 128);
+        mbar_wait(&s_full[h], (uint32_t)t & 1u);
+        tc_fence_after_sync();
+        uint32_t r[2][32];
+        tmem_ld_32x32b_x32(taddr, r[0]);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          tmem_ld_wait();
+          if (c < 3) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+          const uint32_t* v = r[c & 1];
+          uint32_t packed[16];
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            float e0, e1;
+            if (e < kPolyPerChunk) {
+              exp_poly2<3>(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), e0, e1);
+            } else {
+              float y0, y1;
+              unpack2(mul2(pack2(__uint_as_float(v[e]), __uint_as_float(v[e + 1])), pack2(kLog2e, kLog2e)), y0, y1);
+              e0 = ex2_approx(y0);
+              e1 = ex2_approx(y1);
+            }
+            const uint64_t w = add2(rinv2, *reinterpret_cast<const uint64_t*>(&cs[c * 32 + e]));
+            float p0, p1;
+            unpack2(mul2(pack2(e0, e1), w), p0, p1);
+            packed[e >> 1] = bf16x2_bits(p0, p1);
+          }
+          uint8_t* panel = P + (uint32_t)(c >> 1) * kPanelBytes;
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            *reinterpret_cast<uint4*>(panel + sw128_offset((uint32_t)i, (uint32_t)((c & 1) * 4 + g))) =
+                make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+        }
+        tc_fence_before_sync();
+        fence_proxy_async_smem();
+        mbar_arrive(&p_full[h]);
+      }
+      if (ntiles > 0) {
+        mbar_wait(d_full, 0);
+        tc_fence_after_sync();
+      }
+      // ---- final: dA accumulator -> global (every lane loads: tcgen05.ld is warp-collective) ----
+      const float s = args.scale * (args.gscale ? args.gscale[0] : 1.0f);
+      const uint32_t daddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(kH + h) * kTile;
+      const int64_t prow = sd.diag_offset + row;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        if (ntiles > 0) {
+          tmem_ld_32x32b_x32(daddr + c * 32, r);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) r[e] = 0u;
+        }
+        if (row < sd.Ma) {
+          if (args.direct) {
+            float* dst = sd.out + row * kDim + c * 32;
+            const __nv_bfloat16* bp = sd.b + prow * kDim + c * 32;
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              const uint2 braw = *reinterpret_cast<const uint2*>(bp + e);
+              const __nv_bfloat162 b01 = *reinterpret_cast<const __nv_bfloat162*>(&braw.x);
+              const __nv_bfloat162 b23 = *reinterpret_cast<const __nv_bfloat162*>(&braw.y);
+              float4 o;
+              o.x = s * (__uint_as_float(r[e]) - 2.0f * __low2float(b01));
+              o.y = s * (__uint_as_float(r[e + 1]) - 2.0f * __high2float(b01));
+              o.z = s * (__uint_as_float(r[e + 2]) - 2.0f * __low2float(b23));
+              o.w = s * (__uint_as_float(r[e + 3]) - 2.0f * __high2float(b23));
+              *reinterpret_cast<float4*>(dst + e) = o;
+            }
+          } else {
+            float* dst = sd.out + ((int64_t)blockIdx.y * sd.Ma + row) * kDim + c * 32;
+#pragma unroll
+            for (int e = 0; e < 32; e += 4)
+              *reinterpret_cast<float4*>(dst + e) = make_float4(__uint_as_float(r[e]), __uint_as_float(r[e + 1]),
+                                                                __uint_as_float(r[e + 2]), __uint_as_float(r[e + 3]));
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    __syncwarp();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// =================================================================================================================
+// single-pass sum-exp: rowsum_i = sum_j exp(a_i . b_j) (fp32, exact exps), colsum_j = sum_{i != pos(j)} bf16(exp(a_i . b_j))
+// over THIS launch's rows (the diagonal term is added back in fp32 by the finalize kernel), diag_i = a_i . b_(off+i).
+// CTA = 128 rows; 8 epilogue warps = 4 lane quadrants x 2 column halves.
+// =================================================================================================================
+struct Tc2FwdArgs {
+  int64_t Ma, Nb, diag_offset;
+  float* rowpart;   // [2 * nsplit][Ma]  (two column halves per split)
+  float* colpart;   // [row blocks][Nb]
+  float* diag;      // [Ma]
+  int tiles_per_split;
+};
+
+namespace c2 {
+constexpr int kFwdStages = 3;
+constexpr uint32_t kOnesBytes = 2 * 2048;   // B operand of the column-sum MMA: [16 x 128] bf16 ones, two K panels
+// A | Y ring | E x2 | ones | barriers
+constexpr uint32_t kFwdSmem = kTileBytes * (1 + kFwdStages + 2) + kOnesBytes + 256 + 1024;
+static_assert(kFwdSmem <= 232448, "shared memory budget");
+constexpr int kFwdPoly = 14;  // of every 32 exps, this many on the FMA pipes (degree 4)
+}  // namespace c2
+
+__global__ void __launch_bounds__(c2::kThreads, 1)
+tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant__ CUtensorMap tb, const Tc2FwdArgs args) {
+  using namespace c2;
+  const int64_t row0 = (int64_t)blockIdx.x * kTile;
+  const int ntiles_all = (int)((args.Nb + kTile - 1) / kTile);
+  const int tile_begin = blockIdx.y * args.tiles_per_split;
+  const int ntiles = max(min(tile_begin + args.tiles_per_split, ntiles_all) - tile_begin, 0);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_tile = smem;
+  uint8_t* y_tiles = a_tile + kTileBytes;
+  uint8_t* e_tiles = y_tiles + kFwdStages * kTileBytes;   // [2]
+  uint8_t* ones = e_tiles + 2 * kTileBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ones + kOnesBytes);
+  uint64_t* a_full = bars;                   // 1
+  uint64_t* y_full = a_full + 1;             // kFwdStages
+  uint64_t* y_empty = y_full + kFwdStages;   // kFwdStages
+  uint64_t* s_full = y_empty + kFwdStages;   // 2
+  uint64_t* s_empty = s_full + 2;            // 2
+  uint64_t* e_full = s_empty + 2;            // 2
+  uint64_t* e_empty = e_full + 2;            // 2
+  uint64_t* c_full = e_empty + 2;            // 2
+  uint64_t* c_empty = c_full + 2;            // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(a_full, 1);
+    for (int i = 0; i < kFwdStages; ++i) {
+      mbar_init(&y_full[i], 1);
+      mbar_init(&y_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&s_empty[i], 256);
+      mbar_init(&e_full[i], 256);
+      mbar_init(&e_empty[i], 1);
+      mbar_init(&c_full[i], 1);
+      mbar_init(&c_empty[i], 128);
+    }
+    fence_mbar_init();
+  }
+  for (uint32_t o = threadIdx.x * 4u; o < kOnesBytes; o += kThreads * 4u) *reinterpret_cast<uint32_t*>(ones + o) = 0x3F803F80u;
+  fence_proxy_async_smem();
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;     // [0,256): S double buffer; [256, 288): column sums, 16 columns x 2
+  const uint32_t tmem_c = tmem_base + 2 * kTile;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(&ta);
+      tma_prefetch_desc(&tb);
+      mbar_arrive_expect_tx(a_full, kTileBytes);
+      tma_load_2d(a_tile, &ta, a_full, 0, (int32_t)row0);
+      tma_load_2d(a_tile + kPanelBytes, &ta, a_full, 64, (int32_t)row0);
+      for (int t = 0; t < ntiles; ++t) {
+        const int stage = t % kFwdStages;
+        mbar_wait(&y_empty[stage], ((uint32_t)(t / kFwdStages) & 1u) ^ 1u);
+        mbar_arrive_expect_tx(&y_full[stage], kTileBytes);
+        const int32_t col0 = (tile_begin + t) * kTile;
+        uint8_t* dst = y_tiles + (size_t)stage * kTileBytes;
+        tma_load_2d(dst, &tb, &y_full[stage], 0, col0);
+        tma_load_2d(dst + kPanelBytes, &tb, &y_full[stage], 64, col0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && ntiles > 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, 0, 0);  // S = A . Y^T
+      constexpr uint32_t idesc_c = make_idesc_bf16(kTile, 16, 1, 0);     // C[col, :] = sum_rows E[row, col] (E^T . ones)
+      const uint32_t a_addr = smem_u32(a_tile), ones_addr = smem_u32(ones);
+      mbar_wait(a_full, 0);
+      auto issue_s = [&](int t) {
+        const int stage = t % kFwdStages, buf = t & 1;
+        mbar_wait(&s_empty[buf], ((uint32_t)(t >> 1) & 1u) ^ 1u);
+        mbar_wait(&y_full[stage], (uint32_t)(t / kFwdStages) & 1u);
+        tc_fence_after_sync();
+        const uint32_t y_addr = smem_u32(y_tiles + (size_t)stage * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_bf16_ss(tmem_base + (uint32_t)buf * kTile, kmajor_desc(a_addr, k), kmajor_desc(y_addr, k), idesc_s,
+                       k > 0 ? 1u : 0u);
+        umma_commit(&y_empty[stage]);
+        umma_commit(&s_full[buf]);
+      };
+      issue_s(0);
+      for (int t = 0; t < ntiles; ++t) {
+        if (t + 1 < ntiles) issue_s(t + 1);
+        const int buf = t & 1;
+        const uint32_t ph = (uint32_t)(t >> 1) & 1u;
+        mbar_wait(&c_empty[buf], ph ^ 1u);
+        mbar_wait(&e_full[buf], ph);
+        tc_fence_after_sync();
+        const uint32_t e_addr = smem_u32(e_tiles + (size_t)buf * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_bf16_ss(tmem_c + (uint32_t)buf * 16u, mnmajor_desc(e_addr, k),
+                       make_smem_desc_sw128(ones_addr + (uint32_t)(k >> 2) * 2048u + (uint32_t)(k & 3) * 32u, 16, 1024),
+                       idesc_c, k > 0 ? 1u : 0u);
+        umma_commit(&e_empty[buf]);
+        umma_commit(&c_full[buf]);
+      }
+    }
+  } else {
+    const int half = (warp - 2) >> 2, q = warp & 3;
+    const int i = q * 32 + lane;
+    const int64_t row = row0 + i;
+    const int64_t drow = args.diag_offset + row;                       // my positive's column
+    const int64_t dlo = args.diag_offset + row0, dhi = dlo + kTile;    // diagonal band of this row block
+    const bool tail_rows = row0 + kTile > args.Ma;
+    float rs0 = 0.f, rs1 = 0.f, dval = 0.f;
+    bool dfound = false;
+    float* colpart = args.colpart + (int64_t)blockIdx.x * args.Nb;
+    auto flush_cols = [&](int t) {   // column sums of tile t: TMEM lane == column; read by the half-0 warps
+      const int buf = t & 1;
+      mbar_wait(&c_full[buf], (uint32_t)(t >> 1) & 1u);
+      tc_fence_after_sync();
+      uint32_t v;
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v)
+                   : "r"(tmem_c + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 16u) : "memory");
+      tmem_ld_wait();
+      const int64_t col = (int64_t)(tile_begin + t) * kTile + i;
+      if (col < args.Nb) colpart[col] = __uint_as_float(v);
+      tc_fence_before_sync();
+      mbar_arrive(&c_empty[buf]);
+    };
+    for (int t = 0; t < ntiles; ++t) {
+      const int buf = t & 1;
+      const uint32_t ph = (uint32_t)(t >> 1) & 1u;
+      const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
+      const bool special = tail_rows || (col0 + kTile > args.Nb) || (col0 < dhi && col0 + kTile > dlo);
+      uint8_t* E = e_tiles + (size_t)buf * kTileBytes;
+      mbar_wait(&s_full[buf], ph);
+      tc_fence_after_sync();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * kTile + (uint32_t)half * 64u;
+      uint32_t r[2][32];
+      tmem_ld_32x32b_x32(taddr, r[0]);
+      mbar_wait(&e_empty[buf], ph ^ 1u);          // the column-sum MMA of tile t-2 has consumed this E buffer
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        tmem_ld_wait();
+        if (c == 0) tmem_ld_32x32b_x32(taddr + 32, r[1]);
+        const uint32_t* v = r[c];
+        uint32_t packed[16];
+        if (!special) {
+          uint64_t acc = pack2(0.f, 0.f);
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            float e0, e1;
+            if (e < kFwdPoly) {
+              exp_poly2<4>(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), e0, e1);
+            } else {
+              float y0, y1;
+              unpack2(mul2(pack2(__uint_as_float(v[e]), __uint_as_float(v[e + 1])), pack2(kLog2e, kLog2e)), y0, y1);
+              e0 = ex2_approx(y0);
+              e1 = ex2_approx(y1);
+            }
+            acc = add2(acc, pack2(e0, e1));
+            packed[e >> 1] = bf16x2_bits(e0, e1);
+          }
+          float a0, a1;
+          unpack2(acc, a0, a1);
+          rs0 += a0;
+          rs1 += a1;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            float ev[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int64_t col = col0 + half * 64 + c * 32 + e + u;
+              const float s = __uint_as_float(v[e + u]);
+              float x = (col < args.Nb && row < args.Ma) ? ex2_approx(s * kLog2e) : 0.f;
+              if (col < args.Nb) rs0 += x;
+              if (col == drow) {       // keep the positive out of the bf16 column sum: finalize adds it in fp32
+                dval = s;
+                dfound = true;
+                x = 0.f;
+              }
+              ev[u] = x;
+            }
+            packed[e >> 1] = bf16x2_bits(ev[0], ev[1]);
+          }
+        }
+        uint8_t* panel = E + (uint32_t)half * kPanelBytes;   // column half == 64-column panel
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          *reinterpret_cast<uint4*>(panel + sw128_offset((uint32_t)i, (uint32_t)(c * 4 + g))) =
+              make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+      }
+      tc_fence_before_sync();
+      mbar_arrive(&s_empty[buf]);
+      fence_proxy_async_smem();
+      mbar_arrive(&e_full[buf]);
+      if (half == 0 && t > 0) flush_cols(t - 1);   // one tile behind: never waits on the MMA just requested
+    }
+    if (half == 0 && ntiles > 0) flush_cols(ntiles - 1);
+    if (row < args.Ma) {
+      args.rowpart[((int64_t)blockIdx.y * 2 + half) * args.Ma + row] = rs0 + rs1;
+      if (dfound) args.diag[row] = dval;
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    __syncwarp();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// =================================================================================================================
+// host side
+// =================================================================================================================
+__global__ void grad_reduce_kernel(const float* __restrict__ partial, int nsplit, int64_t Ma, int64_t diag_offset,
+                                   const __nv_bfloat16* __restrict__ b, float scale, const float* __restrict__ gscale,
+                                   float* __restrict__ da);
+__global__ void sum_partials_kernel(const float* __restrict__ partial, int nsplit, int64_t M, float* __restrict__ out);
+
+// colsum[j] = sum_r colpart[r][j] + exp(diag[j - off]) for the columns that are some local row's positive
+__global__ void col_reduce_kernel(const float* __restrict__ colpart, int nrb, int64_t Nb, const float* __restrict__ diag,
+                                  int64_t off, int64_t Ma, float* __restrict__ colsum) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= Nb) return;
+  float s = 0.f;
+  for (int r = 0; r < nrb; ++r) s += colpart[(int64_t)r * Nb + j];
+  if (j >= off && j < off + Ma) s += expf(diag[j - off]);
+  colsum[j] = s;
+}
+
+static void plan2(int64_t row_blocks, int64_t ntiles, int n_sides, int max_split, int* nsplit, int* tps) {
+  int64_t want = ceil_div(2 * 148, row_blocks * n_sides);
+  want = std::min<int64_t>(std::min<int64_t>(want, ntiles), max_split);
+  if (want < 1 || ntiles <= 2) want = 1;
+  *tps = (int)ceil_div(ntiles, want);
+  *nsplit = (int)ceil_div(ntiles, *tps);
+}
+
+size_t tc2_grad_workspace(int64_t Ma, int64_t Nb) {
+  int ns, tps;
+  plan2(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 1, 8, &ns, &tps);
+  return ns > 1 ? 2 * align_up((size_t)ns * Ma * c2::kDim * sizeof(float), 1024) + 2048 : 2048;
+}
+
+int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, const float* gscale, void* ws,
+             size_t ws_bytes, cudaStream_t st) {
+  using namespace c2;
+  PCLIP_REQUIRE(D == kDim, PCLIP_ERR_UNSUPPORTED, "bf16 tensor-core path needs D == %d (got %d)", kDim, D);
+  for (int i = 0; i < n_sides; ++i) {
+    const pclip_clip_bwd_side_t& s = sides[i];
+    PCLIP_REQUIRE(s.a && s.b && s.rinv && s.cinv && s.da && s.Ma > 0 && s.Nb > 0, PCLIP_ERR_INVALID, "grad: bad side %d", i);
+    PCLIP_REQUIRE(s.diag_offset >= 0 && s.diag_offset + s.Ma <= s.Nb, PCLIP_ERR_INVALID,
+                  "grad: positives of side %d fall outside b", i);
+    PCLIP_REQUIRE(s.Ma == sides[0].Ma && s.Nb == sides[0].Nb, PCLIP_ERR_UNSUPPORTED,
+                  "grad: both sides must have the same shape");
+  }
+  const int64_t Ma = sides[0].Ma, Nb = sides[0].Nb;
+  int nsplit, tps;
+  plan2(ceil_div(Ma, kRows), ceil_div(Nb, kTile), n_sides, 8, &nsplit, &tps);
+  Workspace w(ws, ws_bytes);
+  Tc2BwdArgs args;
+  CUtensorMap maps[4];
+  float* partial[2] = {nullptr, nullptr};
+  for (int i = 0; i < 2; ++i) {
+    const pclip_clip_bwd_side_t& s = sides[i < n_sides ? i : 0];
+    PCLIP_TRY(make_tmap_bf16_2d(&maps[2 * i], s.a, (uint64_t)s.Ma, kDim, kDim, kTile, 64));
+    PCLIP_TRY(make_tmap_bf16_2d(&maps[2 * i + 1], s.b, (uint64_t)s.Nb, kDim, kDim, kTile, 64));
+    if (nsplit > 1 && i < n_sides) {
+      PCLIP_REQUIRE(ws, PCLIP_ERR_WORKSPACE, "grad: workspace required");
+      partial[i] = w.take<float>((size_t)nsplit * s.Ma * kDim);
+    }
+    args.s[i] = {s.Ma,   s.Nb,   s.diag_offset, s.rinv, s.cinv, static_cast<const __nv_bfloat16*>(s.b),
+                 nsplit > 1 ? partial[i] : s.da};
+  }
+  PCLIP_REQUIRE(nsplit == 1 || w.ok(), PCLIP_ERR_WORKSPACE, "grad: workspace too small");
+  args.tiles_per_split = tps;
+  args.direct = nsplit == 1;
+  args.scale = scale;
+  args.gscale = gscale;
+  PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc2_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmem));
+  dim3 grid((unsigned)ceil_div(Ma, kRows), (unsigned)nsplit, (unsigned)n_sides);
+  tc2_grad_kernel<<<grid, kThreads, kBwdSmem, st>>>(maps[0], maps[1], maps[2], maps[3], args);
+  PCLIP_CHECK_LAUNCH();
+  if (nsplit > 1) {
+    for (int i = 0; i < n_sides; ++i) {
+      grad_reduce_kernel<<<(unsigned)ceil_div(Ma * (kDim / 4), 256), 256, 0, st>>>(
+          partial[i], nsplit, Ma, sides[i].diag_offset, static_cast<const __nv_bfloat16*>(sides[i].b), scale, gscale,
+          sides[i].da);
+      PCLIP_CHECK_LAUNCH();
+    }
+  }
+  return PCLIP_OK;
+}
+
+static void plan_fwd2(int64_t Ma, int64_t Nb, int* nsplit, int* tps) {
+  plan2(ceil_div(Ma, c2::kTile), ceil_div(Nb, c2::kTile), 1, 64, nsplit, tps);
+}
+
+size_t tc2_sumexp_workspace(int64_t Ma, int64_t Nb) {
+  int ns, tps;
+  plan_fwd2(Ma, Nb, &ns, &tps);
+  return align_up((size_t)2 * ns * Ma * sizeof(float), 1024) +
+         align_up((size_t)ceil_div(Ma, c2::kTile) * Nb * sizeof(float), 1024) + 2048;
+}
+
+int tc2_sumexp(const void* a, const void* b, int64_t Ma, int64_t Nb, int64_t diag_offset, int D, float* rowsum,
+               float* colsum, float* diag, void* ws, size_t ws_bytes, cudaStream_t st) {
+  using namespace c2;
+  PCLIP_REQUIRE(D == kDim, PCLIP_ERR_UNSUPPORTED, "bf16 tensor-core path needs D == %d (got %d)", kDim, D);
+  int nsplit, tps;
+  plan_fwd2(Ma, Nb, &nsplit, &tps);
+  const int nrb = (int)ceil_div(Ma, kTile);
+  Workspace w(ws, ws_bytes);
+  float* rowpart = w.take<float>((size_t)2 * nsplit * Ma);
+  float* colpart = w.take<float>((size_t)nrb * Nb);
+  PCLIP_REQUIRE(ws && w.ok(), PCLIP_ERR_WORKSPACE, "sumexp: workspace too small");
+  CUtensorMap ma, mb;
+  PCLIP_TRY(make_tmap_bf16_2d(&ma, a, (uint64_t)Ma, kDim, kDim, kTile, 64));
+  PCLIP_TRY(make_tmap_bf16_2d(&mb, b, (uint64_t)Nb, kDim, kDim, kTile, 64));
+  Tc2FwdArgs args{Ma, Nb, diag_offset, rowpart, colpart, diag, tps};
+  PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc2_sumexp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+  dim3 grid((unsigned)nrb, (unsigned)nsplit);
+  tc2_sumexp_kernel<<<grid, kThreads, kFwdSmem, st>>>(ma, mb, args);
+  PCLIP_CHECK_LAUNCH();
+  sum_partials_kernel<<<(unsigned)ceil_div(Ma, 256), 256, 0, st>>>(rowpart, 2 * nsplit, Ma, rowsum);
+  PCLIP_CHECK_LAUNCH();
+  col_reduce_kernel<<<(unsigned)ceil_div(Nb, 256), 256, 0, st>>>(colpart, nrb, Nb, diag, diag_offset, Ma, colsum);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+}  // namespace pclip
