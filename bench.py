@@ -201,8 +201,8 @@ class ClipLarge:
     def config(self):
         return {"workload": self.name, "B": self.B, "D": self.D, "compute": "bf16 tcgen05, fp32 accumulate",
                 "sharding": f"rows/{self.dist.world} + all-gather" if self.dist.on else "single GPU",
-                "l2": "no flush: per-step working set ~235 MB (fp32 in 67, bf16 packed+transposed 67, fp32 grads 67, "
-                      "gathered copies) > 126 MB L2"}
+                "l2": "no flush: per-step working set ~300 MB (fp32 in 67, bf16 packed 34, fp32 grads 67, column-sum "
+                      "partials 134) > 126 MB L2"}
 
     def roofline(self, peaks, steps):
         ev = self.events
@@ -212,11 +212,11 @@ class ClipLarge:
         Ma, B, D = self.Ma, self.B, self.D
         flops = 4.0 * Ma * B * D                         # dX and dY GEMMs of this rank's rows (algorithmic)
         ach = flops / (out["grad"] * 1e-3) / 1e12
-        return {"bound": "tensor", "kernel": "tc_grad_kernel", "achieved": round(ach, 1), "peak": peaks["tc"],
+        return {"bound": "tensor", "kernel": "tc2_grad_kernel", "achieved": round(ach, 1), "peak": peaks["tc"],
                 "unit": "TFLOP/s", "frac": round(ach / peaks["tc"], 4), "traffic": None,
                 "peak_source": f"{peaks['src']} bf16_tflops_sustained",
                 "algorithmic_flops_per_launch": flops, "kernel_ms": round(out["grad"], 4),
-                "other_kernels_ms": {"tc_rowsumexp_kernel": round(out["rowsumexp"], 4)}}
+                "other_kernels_ms": {"tc2_sumexp_kernel (+2 small reduces)": round(out["rowsumexp"], 4)}}
 
     def cpu_sample(self, budget_s=12.0):
         """Oracle port on the host cores: rows [0, n) of the same B = 65 536 workload in fp32 (n / B of one

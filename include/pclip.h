@@ -111,6 +111,18 @@ size_t pclip_clip_rowsumexp_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, i
 int pclip_clip_rowsumexp(const pclip_clip_fwd_side_t* sides /* HOST */, int32_t n_sides /* 1 or 2 */, int32_t D,
                          int32_t compute, void* workspace, size_t workspace_bytes, pclip_stream_t stream);
 
+/* Single-pass variant (bf16 compute only): one sweep over S = a b^T gives
+ *   rowsum[i] = sum_j exp(a_i . b_j)                 (i < Ma; complete)
+ *   colsum[j] = sum_{i < Ma} exp(a_i . b_j)          (j < Nb; partial over THIS call's rows: a row-sharded job
+ *                                                     all-reduces it)
+ *   diag[i]   = a_i . b_(diag_offset + i)
+ * ref: modules/training_utils.py:85-88 (exp_logits.sum(1) and exp_logits.sum(0) of ONE logits matrix). */
+size_t pclip_clip_sumexp_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, int32_t compute);
+int pclip_clip_sumexp(const void* a /* [Ma,D] bf16 */, const void* b /* [Nb,D] bf16 */, int64_t Ma, int64_t Nb,
+                      int64_t diag_offset, int32_t D, int32_t compute, float* rowsum /* [Ma] */,
+                      float* colsum /* [Nb] */, float* diag /* [Ma] */, void* workspace, size_t workspace_bytes,
+                      pclip_stream_t stream);
+
 /* per-row loss terms -> row_lse/col_lse, 1/R, 1/C and loss[0] (+)= scale * sum_i(log R_i + log C_i - 2 diag_i) */
 int pclip_clip_finalize(const float* rowsum, const float* colsum, const float* diag, int64_t M, float scale,
                         float* row_lse, float* col_lse, float* rinv, float* cinv, float* loss /* [1] */,

@@ -84,7 +84,8 @@ size_t pclip_clip_workspace_bytes(int64_t B, int32_t D, int32_t compute) {
   size_t n = 2 * align_up((size_t)B * D * esz, 1024) + 8 * align_up((size_t)B * sizeof(float), 1024);
   if (tc) {
     n += 2 * align_up((size_t)D * ld_transposed(B) * esz, 1024);
-    const size_t a = tc_rowsumexp_workspace(B, B), b = tc_grad_workspace(B, B);
+    const size_t a = std::max(tc_rowsumexp_workspace(B, B), tc2_sumexp_workspace(B, B));
+    const size_t b = std::max(tc_grad_workspace(B, B), tc2_grad_workspace(B, B));
     n += align_up(a > b ? a : b, 1024);
   }
   return n + 16 * 1024;
@@ -98,6 +99,23 @@ int pclip_clip_rowsumexp(const pclip_clip_fwd_side_t* sides, int32_t n_sides, in
   if (compute == PCLIP_COMPUTE_BF16) return tc_rowsumexp(sides, n_sides, D, workspace, workspace_bytes, st);
   if (compute == PCLIP_COMPUTE_F32) return simt_rowsumexp(sides, n_sides, D, st);
   return fail(PCLIP_ERR_UNSUPPORTED, "rowsumexp: unknown compute mode %d", compute);
+}
+
+size_t pclip_clip_sumexp_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, int32_t compute) {
+  (void)D;
+  return compute == PCLIP_COMPUTE_BF16 ? tc2_sumexp_workspace(Ma, Nb) : 0;
+}
+
+int pclip_clip_sumexp(const void* a, const void* b, int64_t Ma, int64_t Nb, int64_t diag_offset, int32_t D,
+                      int32_t compute, float* rowsum, float* colsum, float* diag, void* workspace,
+                      size_t workspace_bytes, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(a && b && rowsum && colsum && diag && Ma > 0 && Nb > 0, PCLIP_ERR_INVALID, "sumexp: null argument");
+  PCLIP_REQUIRE(diag_offset >= 0 && diag_offset + Ma <= Nb, PCLIP_ERR_INVALID, "sumexp: positives fall outside b");
+  PCLIP_REQUIRE(compute == PCLIP_COMPUTE_BF16, PCLIP_ERR_UNSUPPORTED,
+                "sumexp: single-pass forward exists for bf16 compute only (use pclip_clip_rowsumexp)");
+  return tc2_sumexp(a, b, Ma, Nb, diag_offset, D, rowsum, colsum, diag, workspace, workspace_bytes,
+                    static_cast<cudaStream_t>(stream));
 }
 
 int pclip_clip_grad(const pclip_clip_bwd_side_t* sides, int32_t n_sides, int32_t D, int32_t compute, float scale,
@@ -138,7 +156,7 @@ int pclip_clip_loss(const pclip_chunk_t* x_chunks, int32_t nx, const pclip_chunk
   char* Y = ws.take<char>((size_t)B * D * esz);
   char* XT = nullptr;
   char* YT = nullptr;
-  if (tc && want_grad) {
+  if (tc && want_grad && clip_generation() == 1) {  // only the first-generation gradient kernel reads transposes
     XT = ws.take<char>((size_t)D * ldT * esz);
     YT = ws.take<char>((size_t)D * ldT * esz);
   }
@@ -156,8 +174,14 @@ int pclip_clip_loss(const pclip_chunk_t* x_chunks, int32_t nx, const pclip_chunk
   PCLIP_REQUIRE(ws.ok(), PCLIP_ERR_WORKSPACE, "clip_loss: workspace overflow");
 
   PCLIP_TRY(pack_operands(x_chunks, nx, y_chunks, ny, in_dtype, B, D, cdt, X, XT, Y, YT, ldT, st));
-  pclip_clip_fwd_side_t f[2] = {{X, Y, B, B, 0, rowsum, diag}, {Y, X, B, B, 0, colsum, diag2}};
-  PCLIP_TRY(pclip_clip_rowsumexp(f, 2, D, compute, scratch, scratch_bytes, stream));
+  // below 2048 columns the two-sided forward keeps the column sums fp32-exact (the single pass sums bf16-rounded
+  // exps: the rounding averages out over thousands of rows, not over 16)
+  if (tc && clip_generation() != 1 && B >= 2048) {
+    PCLIP_TRY(pclip_clip_sumexp(X, Y, B, B, 0, D, compute, rowsum, colsum, diag, scratch, scratch_bytes, stream));
+  } else {
+    pclip_clip_fwd_side_t f[2] = {{X, Y, B, B, 0, rowsum, diag}, {Y, X, B, B, 0, colsum, diag2}};
+    PCLIP_TRY(pclip_clip_rowsumexp(f, 2, D, compute, scratch, scratch_bytes, stream));
+  }
   const float scale = 0.5f / (float)B;
   PCLIP_TRY(pclip_clip_finalize(rowsum, colsum, diag, B, scale, rl, cl, rinv, cinv, loss, stream));
   if (want_grad) {

@@ -11,9 +11,18 @@
 //   * tc2_sumexp_kernel is single-pass: row sums in-thread, column sums by a third, M = 64 "ones" MMA over the bf16
 //     exp tile (the tile is the MN-major B operand), instead of recomputing the transposed score matrix.
 #include <cuda_bf16.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "ptx.cuh"
+
+#ifndef PCLIP_FWD_POLY
+#define PCLIP_FWD_POLY 14
+#endif
+#ifndef PCLIP_BWD_POLY
+#define PCLIP_BWD_POLY 8
+#endif
 
 namespace pclip {
 namespace c2 {
@@ -58,6 +67,11 @@ __device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
+__device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
 __device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
   uint64_t d;
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
@@ -71,8 +85,8 @@ __device__ __forceinline__ void exp_poly2(float x0, float x1, float& e0, float& 
   const uint64_t x = pack2(x0, x1);
   const uint64_t l2 = pack2(kLog2e, kLog2e);
   const uint64_t t = fma2(x, l2, pack2(kMagic, kMagic));
-  const uint64_t n = add2(t, pack2(-kMagic, -kMagic));
-  const uint64_t f = fma2(x, l2, mul2(n, pack2(-1.0f, -1.0f)));
+  const uint64_t nn = sub2(pack2(kMagic, kMagic), t);   // -n
+  const uint64_t f = fma2(x, l2, nn);
   uint64_t p;
   if (kDegree == 3) {
     p = fma2(f, pack2(0.055171459913253784f, 0.055171459913253784f), pack2(0.2426108568906784f, 0.2426108568906784f));
@@ -121,10 +135,11 @@ constexpr int kBwdStages = 3;
 // A (2 tiles) | Y ring | P (2 tiles) | cinv staging [2][128] | barriers
 constexpr uint32_t kBwdSmem = kTileBytes * (kH + kBwdStages + kH) + 2 * kTile * 4 + 256 + 1024;
 static_assert(kBwdSmem <= 232448, "shared memory budget");
-constexpr int kPolyPerChunk = 8;  // of every 32 exps, this many go to the FMA pipes (multiple of 2)
+constexpr int kBwdThreads = 64 + 32 * 16;
+constexpr int kPolyPerChunk = PCLIP_BWD_POLY;  // of every 32 exps, this many go to the FMA pipes (multiple of 2)
 }  // namespace c2
 
-__global__ void __launch_bounds__(c2::kThreads, 1)
+__global__ void __launch_bounds__(c2::kBwdThreads, 1)
 tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__ CUtensorMap tb0,
                 const __grid_constant__ CUtensorMap ta1, const __grid_constant__ CUtensorMap tb1,
                 const Tc2BwdArgs args) {
@@ -165,7 +180,7 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
     }
     for (int i = 0; i < kH; ++i) {
       mbar_init(&s_full[i], 1);
-      mbar_init(&p_full[i], 128);
+      mbar_init(&p_full[i], 256);
     }
     mbar_init(d_full, 1);
     fence_mbar_init();
@@ -237,29 +252,28 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
       umma_commit(d_full);
     }
   } else {
-    const int h = (warp - 2) >> 2, q = warp & 3;
+    // 16 epilogue warps: row half h x lane quadrant q x column half ch (4 warps per SM sub-partition)
+    const int h = (warp - 2) >> 3, ch = ((warp - 2) >> 2) & 1, q = warp & 3;
     const int i = q * 32 + lane;                       // row inside the tile
     const int64_t row = row0 + h * kTile + i;
     const bool live = h < nh;
     if (live) {
       const float rinv = row < sd.Ma ? sd.rinv[row] : 0.f;
       const uint64_t rinv2 = pack2(rinv, rinv);
-      uint8_t* P = p_tiles + h * kTileBytes;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)h * kTile;
+      const uint32_t p_addr = smem_u32(p_tiles + h * kTileBytes) + (uint32_t)ch * kPanelBytes;   // my 64-column panel
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)h * kTile + (uint32_t)ch * 64u;
       for (int t = 0; t < ntiles; ++t) {
         const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
         float* cs = cinv_s + (t & 1) * kTile;
-        cs[i] = (col0 + i < sd.Nb) ? sd.cinv[col0 + i] : 0.f;   // 0 also masks the zero-filled columns beyond Nb
-        named_bar_sync(1 + h, 128);
+        if (ch == 0) cs[i] = (col0 + i < sd.Nb) ? sd.cinv[col0 + i] : 0.f;   // 0 also masks the zero-filled columns beyond Nb
+        named_bar_sync(1 + h, 256);
         mbar_wait(&s_full[h], (uint32_t)t & 1u);
         tc_fence_after_sync();
-        uint32_t r[2][32];
-        tmem_ld_32x32b_x32(taddr, r[0]);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, v);
           tmem_ld_wait();
-          if (c < 3) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
-          const uint32_t* v = r[c & 1];
           uint32_t packed[16];
 #pragma unroll
           for (int e = 0; e < 32; e += 2) {
@@ -272,16 +286,15 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
               e0 = ex2_approx(y0);
               e1 = ex2_approx(y1);
             }
-            const uint64_t w = add2(rinv2, *reinterpret_cast<const uint64_t*>(&cs[c * 32 + e]));
+            const uint64_t w = add2(rinv2, *reinterpret_cast<const uint64_t*>(&cs[ch * 64 + c * 32 + e]));
             float p0, p1;
             unpack2(mul2(pack2(e0, e1), w), p0, p1);
             packed[e >> 1] = bf16x2_bits(p0, p1);
           }
-          uint8_t* panel = P + (uint32_t)(c >> 1) * kPanelBytes;
 #pragma unroll
           for (int g = 0; g < 4; ++g)
-            *reinterpret_cast<uint4*>(panel + sw128_offset((uint32_t)i, (uint32_t)((c & 1) * 4 + g))) =
-                make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+            st_shared_v4(p_addr + sw128_offset((uint32_t)i, (uint32_t)(c * 4 + g)), packed[4 * g], packed[4 * g + 1],
+                         packed[4 * g + 2], packed[4 * g + 3]);
         }
         tc_fence_before_sync();
         fence_proxy_async_smem();
@@ -293,10 +306,10 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
       }
       // ---- final: dA accumulator -> global (every lane loads: tcgen05.ld is warp-collective) ----
       const float s = args.scale * (args.gscale ? args.gscale[0] : 1.0f);
-      const uint32_t daddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(kH + h) * kTile;
+      const uint32_t daddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(kH + h) * kTile + (uint32_t)ch * 64u;
       const int64_t prow = sd.diag_offset + row;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
         if (ntiles > 0) {
           tmem_ld_32x32b_x32(daddr + c * 32, r);
@@ -307,8 +320,8 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         }
         if (row < sd.Ma) {
           if (args.direct) {
-            float* dst = sd.out + row * kDim + c * 32;
-            const __nv_bfloat16* bp = sd.b + prow * kDim + c * 32;
+            float* dst = sd.out + row * kDim + ch * 64 + c * 32;
+            const __nv_bfloat16* bp = sd.b + prow * kDim + ch * 64 + c * 32;
 #pragma unroll
             for (int e = 0; e < 32; e += 4) {
               const uint2 braw = *reinterpret_cast<const uint2*>(bp + e);
@@ -322,7 +335,7 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
               *reinterpret_cast<float4*>(dst + e) = o;
             }
           } else {
-            float* dst = sd.out + ((int64_t)blockIdx.y * sd.Ma + row) * kDim + c * 32;
+            float* dst = sd.out + ((int64_t)blockIdx.y * sd.Ma + row) * kDim + ch * 64 + c * 32;
 #pragma unroll
             for (int e = 0; e < 32; e += 4)
               *reinterpret_cast<float4*>(dst + e) = make_float4(__uint_as_float(r[e]), __uint_as_float(r[e + 1]),
@@ -342,90 +355,116 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
 }
 
 // =================================================================================================================
-// single-pass sum-exp: rowsum_i = sum_j exp(a_i . b_j) (fp32, exact exps), colsum_j = sum_{i != pos(j)} bf16(exp(a_i . b_j))
-// over THIS launch's rows (the diagonal term is added back in fp32 by the finalize kernel), diag_i = a_i . b_(off+i).
-// CTA = 128 rows; 8 epilogue warps = 4 lane quadrants x 2 column halves.
+// single-pass sum-exp: rowsum_i = sum_j exp(a_i . b_j) (fp32 exps), colsum_j = sum_{i != pos(j)} bf16(exp(a_i . b_j))
+// over THIS launch's rows (the diagonal term is added back in fp32 by col_reduce_kernel), diag_i = a_i . b_(off+i).
+//
+// CTA = 256 rows (two 128-row A tiles share every streamed column tile: the kernel was bound by the L2 -> SMEM
+// latency of the column tiles with 128-row CTAs, profiles/r01c).  Work items u = (column tile t, row half h).
+//   warp 0      TMA producer (A tiles once, column-tile ring)
+//   warp 1      MMA issuer: S(u) = A_h Y_t^T into one of three TMEM accumulators, and the column-sum MMA
+//               C_t += E(u)^T . ones (M = 128 columns, N = 16, the bf16 exp tile is the MN-major A operand).  It polls
+//               its barriers so that a column-sum MMA never queues behind a wait for a column tile still in flight.
+//   warps 2-17  epilogue: 4 lane quadrants x 4 column quarters; thread = one row x 32 columns of the item.
 // =================================================================================================================
 struct Tc2FwdArgs {
   int64_t Ma, Nb, diag_offset;
-  float* rowpart;   // [2 * nsplit][Ma]  (two column halves per split)
-  float* colpart;   // [row blocks][Nb]
+  float* rowpart;   // [4 * nsplit][Ma]  (four column quarters per split)
+  float* colpart;   // [256-row blocks][Nb]
   float* diag;      // [Ma]
   int tiles_per_split;
+  long long* trace; // debug timeline of CTA (0,0): [8][kTraceItems] SM clocks, or NULL (PCLIP_FWD_TRACE=file)
 };
 
 namespace c2 {
+constexpr int kTraceItems = 96;
 constexpr int kFwdStages = 3;
-constexpr uint32_t kOnesBytes = 2 * 2048;   // B operand of the column-sum MMA: [16 x 128] bf16 ones, two K panels
-// A | Y ring | E x2 | ones | barriers
-constexpr uint32_t kFwdSmem = kTileBytes * (1 + kFwdStages + 2) + kOnesBytes + 256 + 1024;
+constexpr int kSBuf = 3;                    // score accumulators in TMEM
+constexpr uint32_t kOnesBytes = 2048;       // B operand of the column-sum MMA: [16 x 64] bf16 ones (one K panel, reused)
+// A x2 | Y ring | E x2 | ones | barriers
+constexpr uint32_t kFwdSmem = kTileBytes * (kH + kFwdStages + 2) + kOnesBytes + 256 + 768;
 static_assert(kFwdSmem <= 232448, "shared memory budget");
-constexpr int kFwdPoly = 14;  // of every 32 exps, this many on the FMA pipes (degree 4)
+constexpr int kFwdPoly = PCLIP_FWD_POLY;  // of every 32 exps, this many on the FMA pipes (degree 4)
+constexpr int kFwdEpiWarps = 16;          // 4 warps per SM sub-partition
+constexpr int kFwdThreads = 64 + 32 * kFwdEpiWarps;
 }  // namespace c2
 
-__global__ void __launch_bounds__(c2::kThreads, 1)
+#define PCLIP_TRACE(ev, u)                                                                       \
+  do {                                                                                          \
+    if (tr && (u) < kTraceItems) tr[(ev) * kTraceItems + (u)] = clock64();                      \
+  } while (0)
+
+template <int kPoly>
+__global__ void __launch_bounds__(c2::kFwdThreads, 1)
 tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant__ CUtensorMap tb, const Tc2FwdArgs args) {
   using namespace c2;
-  const int64_t row0 = (int64_t)blockIdx.x * kTile;
+  const int64_t row0 = (int64_t)blockIdx.x * kRows;
+  const int nh = row0 + kTile < args.Ma ? 2 : 1;
   const int ntiles_all = (int)((args.Nb + kTile - 1) / kTile);
   const int tile_begin = blockIdx.y * args.tiles_per_split;
   const int ntiles = max(min(tile_begin + args.tiles_per_split, ntiles_all) - tile_begin, 0);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* a_tile = smem;
-  uint8_t* y_tiles = a_tile + kTileBytes;
-  uint8_t* e_tiles = y_tiles + kFwdStages * kTileBytes;   // [2]
+  uint8_t* a_tiles = smem;                                  // [kH]
+  uint8_t* y_tiles = a_tiles + kH * kTileBytes;             // [kFwdStages]
+  uint8_t* e_tiles = y_tiles + kFwdStages * kTileBytes;     // [2], indexed by the row half
   uint8_t* ones = e_tiles + 2 * kTileBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(ones + kOnesBytes);
   uint64_t* a_full = bars;                   // 1
   uint64_t* y_full = a_full + 1;             // kFwdStages
   uint64_t* y_empty = y_full + kFwdStages;   // kFwdStages
-  uint64_t* s_full = y_empty + kFwdStages;   // 2
-  uint64_t* s_empty = s_full + 2;            // 2
-  uint64_t* e_full = s_empty + 2;            // 2
+  uint64_t* s_full = y_empty + kFwdStages;   // kSBuf
+  uint64_t* s_empty = s_full + kSBuf;        // kSBuf
+  uint64_t* e_full = s_empty + kSBuf;        // 2
   uint64_t* e_empty = e_full + 2;            // 2
   uint64_t* c_full = e_empty + 2;            // 2
   uint64_t* c_empty = c_full + 2;            // 2
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c_empty + 2);
+  if (threadIdx.x == 0 && reinterpret_cast<uint8_t*>(tmem_slot + 1) > smem_raw + kFwdSmem) __trap();  // alignment slack
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  long long* tr = (args.trace && blockIdx.x == 0 && blockIdx.y == 0) ? args.trace : nullptr;
   if (threadIdx.x == 0) {
     mbar_init(a_full, 1);
     for (int i = 0; i < kFwdStages; ++i) {
       mbar_init(&y_full[i], 1);
       mbar_init(&y_empty[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kSBuf; ++i) {
       mbar_init(&s_full[i], 1);
-      mbar_init(&s_empty[i], 256);
-      mbar_init(&e_full[i], 256);
+      mbar_init(&s_empty[i], 32 * kFwdEpiWarps);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&e_full[i], 32 * kFwdEpiWarps);
       mbar_init(&e_empty[i], 1);
       mbar_init(&c_full[i], 1);
       mbar_init(&c_empty[i], 128);
     }
     fence_mbar_init();
   }
-  for (uint32_t o = threadIdx.x * 4u; o < kOnesBytes; o += kThreads * 4u) *reinterpret_cast<uint32_t*>(ones + o) = 0x3F803F80u;
+  for (uint32_t o = threadIdx.x * 4u; o < kOnesBytes; o += kFwdThreads * 4u) *reinterpret_cast<uint32_t*>(ones + o) = 0x3F803F80u;
   fence_proxy_async_smem();
   if (warp == 1) tmem_alloc<512>(tmem_slot);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;     // [0,256): S double buffer; [256, 288): column sums, 16 columns x 2
-  const uint32_t tmem_c = tmem_base + 2 * kTile;
+  const uint32_t tmem_base = *tmem_slot;     // [0, 384): three S accumulators; [384, 416): column sums, 16 columns x 2
+  const uint32_t tmem_c = tmem_base + kSBuf * kTile;
 
   if (warp == 0) {
     if (lane == 0) {
       tma_prefetch_desc(&ta);
       tma_prefetch_desc(&tb);
-      mbar_arrive_expect_tx(a_full, kTileBytes);
-      tma_load_2d(a_tile, &ta, a_full, 0, (int32_t)row0);
-      tma_load_2d(a_tile + kPanelBytes, &ta, a_full, 64, (int32_t)row0);
+      mbar_arrive_expect_tx(a_full, (uint32_t)nh * kTileBytes);
+      for (int h = 0; h < nh; ++h) {
+        tma_load_2d(a_tiles + h * kTileBytes, &ta, a_full, 0, (int32_t)(row0 + h * kTile));
+        tma_load_2d(a_tiles + h * kTileBytes + kPanelBytes, &ta, a_full, 64, (int32_t)(row0 + h * kTile));
+      }
       for (int t = 0; t < ntiles; ++t) {
         const int stage = t % kFwdStages;
         mbar_wait(&y_empty[stage], ((uint32_t)(t / kFwdStages) & 1u) ^ 1u);
         mbar_arrive_expect_tx(&y_full[stage], kTileBytes);
+        PCLIP_TRACE(0, t * nh);
         const int32_t col0 = (tile_begin + t) * kTile;
         uint8_t* dst = y_tiles + (size_t)stage * kTileBytes;
         tma_load_2d(dst, &tb, &y_full[stage], 0, col0);
@@ -436,50 +475,61 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
     if (lane == 0 && ntiles > 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, 0, 0);  // S = A . Y^T
       constexpr uint32_t idesc_c = make_idesc_bf16(kTile, 16, 1, 0);     // C[col, :] = sum_rows E[row, col] (E^T . ones)
-      const uint32_t a_addr = smem_u32(a_tile), ones_addr = smem_u32(ones);
+      const uint32_t ones_addr = smem_u32(ones);
+      const int n_items = ntiles * nh;
       mbar_wait(a_full, 0);
-      auto issue_s = [&](int t) {
-        const int stage = t % kFwdStages, buf = t & 1;
-        mbar_wait(&s_empty[buf], ((uint32_t)(t >> 1) & 1u) ^ 1u);
-        mbar_wait(&y_full[stage], (uint32_t)(t / kFwdStages) & 1u);
-        tc_fence_after_sync();
-        const uint32_t y_addr = smem_u32(y_tiles + (size_t)stage * kTileBytes);
+      int us = 0, uc = 0;                       // next score item / next column-sum item
+      int s_t = 0, s_h = 0, c_t = 0, c_h = 0;   // their (tile, half)
+      while (uc < n_items) {
+        // column sums first: they free the E buffer and are short
+        if (uc < us) {
+          bool ready = mbar_test(&e_full[c_h], (uint32_t)c_t & 1u);
+          if (ready && c_h == 0) ready = mbar_test(&c_empty[c_t & 1], ((uint32_t)(c_t >> 1) & 1u) ^ 1u);
+          if (ready) {
+            tc_fence_after_sync();
+            PCLIP_TRACE(2, uc);
+            const uint32_t e_addr = smem_u32(e_tiles + (size_t)c_h * kTileBytes);
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          umma_bf16_ss(tmem_base + (uint32_t)buf * kTile, kmajor_desc(a_addr, k), kmajor_desc(y_addr, k), idesc_s,
-                       k > 0 ? 1u : 0u);
-        umma_commit(&y_empty[stage]);
-        umma_commit(&s_full[buf]);
-      };
-      issue_s(0);
-      for (int t = 0; t < ntiles; ++t) {
-        if (t + 1 < ntiles) issue_s(t + 1);
-        const int buf = t & 1;
-        const uint32_t ph = (uint32_t)(t >> 1) & 1u;
-        mbar_wait(&c_empty[buf], ph ^ 1u);
-        mbar_wait(&e_full[buf], ph);
-        tc_fence_after_sync();
-        const uint32_t e_addr = smem_u32(e_tiles + (size_t)buf * kTileBytes);
+            for (int k = 0; k < 8; ++k)
+              umma_bf16_ss(tmem_c + (uint32_t)(c_t & 1) * 16u, mnmajor_desc(e_addr, k),
+                           make_smem_desc_sw128(ones_addr + (uint32_t)(k & 3) * 32u, 16, 1024), idesc_c,
+                           (c_h > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&e_empty[c_h]);
+            if (c_h == nh - 1) umma_commit(&c_full[c_t & 1]);
+            ++uc;
+            if (++c_h == nh) { c_h = 0; ++c_t; }
+            continue;
+          }
+        }
+        if (us < n_items) {
+          const int sb = us % kSBuf, stage = s_t % kFwdStages;
+          bool ready = mbar_test(&s_empty[sb], ((uint32_t)(us / kSBuf) & 1u) ^ 1u);
+          if (ready && s_h == 0) ready = mbar_test(&y_full[stage], (uint32_t)(s_t / kFwdStages) & 1u);
+          if (ready) {
+            tc_fence_after_sync();
+            PCLIP_TRACE(1, us);
+            const uint32_t y_addr = smem_u32(y_tiles + (size_t)stage * kTileBytes);
+            const uint32_t a_addr = smem_u32(a_tiles + (size_t)s_h * kTileBytes);
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          umma_bf16_ss(tmem_c + (uint32_t)buf * 16u, mnmajor_desc(e_addr, k),
-                       make_smem_desc_sw128(ones_addr + (uint32_t)(k >> 2) * 2048u + (uint32_t)(k & 3) * 32u, 16, 1024),
-                       idesc_c, k > 0 ? 1u : 0u);
-        umma_commit(&e_empty[buf]);
-        umma_commit(&c_full[buf]);
+            for (int k = 0; k < 8; ++k)
+              umma_bf16_ss(tmem_base + (uint32_t)sb * kTile, kmajor_desc(a_addr, k), kmajor_desc(y_addr, k), idesc_s,
+                           k > 0 ? 1u : 0u);
+            if (s_h == nh - 1) umma_commit(&y_empty[stage]);
+            umma_commit(&s_full[sb]);
+            ++us;
+            if (++s_h == nh) { s_h = 0; ++s_t; }
+          }
+        }
       }
     }
   } else {
-    const int half = (warp - 2) >> 2, q = warp & 3;
+    const int quarter = (warp - 2) >> 2, q = warp & 3;                // 32 columns of 32 rows per warp and item
     const int i = q * 32 + lane;
-    const int64_t row = row0 + i;
-    const int64_t drow = args.diag_offset + row;                       // my positive's column
-    const int64_t dlo = args.diag_offset + row0, dhi = dlo + kTile;    // diagonal band of this row block
-    const bool tail_rows = row0 + kTile > args.Ma;
-    float rs0 = 0.f, rs1 = 0.f, dval = 0.f;
-    bool dfound = false;
+    float rs[2] = {0.f, 0.f}, dval[2] = {0.f, 0.f};
+    bool dfound[2] = {false, false};
     float* colpart = args.colpart + (int64_t)blockIdx.x * args.Nb;
-    auto flush_cols = [&](int t) {   // column sums of tile t: TMEM lane == column; read by the half-0 warps
+    const uint32_t e_base = smem_u32(e_tiles);
+    auto flush_cols = [&](int t) {   // column sums of tile t: TMEM lane == column; read by the quarter-0 warps
       const int buf = t & 1;
       mbar_wait(&c_full[buf], (uint32_t)(t >> 1) & 1u);
       tc_fence_after_sync();
@@ -492,80 +542,91 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
       tc_fence_before_sync();
       mbar_arrive(&c_empty[buf]);
     };
+    int sb = 0;
+    uint32_t sph = 0;
     for (int t = 0; t < ntiles; ++t) {
-      const int buf = t & 1;
-      const uint32_t ph = (uint32_t)(t >> 1) & 1u;
       const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
-      const bool special = tail_rows || (col0 + kTile > args.Nb) || (col0 < dhi && col0 + kTile > dlo);
-      uint8_t* E = e_tiles + (size_t)buf * kTileBytes;
-      mbar_wait(&s_full[buf], ph);
-      tc_fence_after_sync();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * kTile + (uint32_t)half * 64u;
-      uint32_t r[2][32];
-      tmem_ld_32x32b_x32(taddr, r[0]);
-      mbar_wait(&e_empty[buf], ph ^ 1u);          // the column-sum MMA of tile t-2 has consumed this E buffer
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_wait();
-        if (c == 0) tmem_ld_32x32b_x32(taddr + 32, r[1]);
-        const uint32_t* v = r[c];
-        uint32_t packed[16];
-        if (!special) {
-          uint64_t acc = pack2(0.f, 0.f);
+      for (int h = 0; h < kH; ++h) {
+        if (h < nh) {
+          const int64_t rb = row0 + h * kTile;                          // first row of this half
+          const int64_t row = rb + i;
+          const int64_t drow = args.diag_offset + row;                  // my positive's column
+          const int64_t dlo = args.diag_offset + rb, dhi = dlo + kTile; // diagonal band of this half
+          const bool special = (rb + kTile > args.Ma) || (col0 + kTile > args.Nb) || (col0 < dhi && col0 + kTile > dlo);
+          mbar_wait(&s_full[sb], sph);
+          tc_fence_after_sync();
+          if (threadIdx.x == 64) PCLIP_TRACE(3, t * nh + h);
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)sb * kTile + (uint32_t)quarter * 32u, v);
+          tmem_ld_wait();
+          tc_fence_before_sync();
+          mbar_arrive(&s_empty[sb]);                // S(u) is in registers: the MMA warp may overwrite the accumulator
+          if (threadIdx.x == 64) PCLIP_TRACE(4, t * nh + h);
+          if (++sb == kSBuf) { sb = 0; sph ^= 1u; }
+          uint32_t packed[16];
+          if (!special) {
+            uint64_t acc = pack2(0.f, 0.f);
 #pragma unroll
-          for (int e = 0; e < 32; e += 2) {
-            float e0, e1;
-            if (e < kFwdPoly) {
-              exp_poly2<4>(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), e0, e1);
-            } else {
-              float y0, y1;
-              unpack2(mul2(pack2(__uint_as_float(v[e]), __uint_as_float(v[e + 1])), pack2(kLog2e, kLog2e)), y0, y1);
-              e0 = ex2_approx(y0);
-              e1 = ex2_approx(y1);
-            }
-            acc = add2(acc, pack2(e0, e1));
-            packed[e >> 1] = bf16x2_bits(e0, e1);
-          }
-          float a0, a1;
-          unpack2(acc, a0, a1);
-          rs0 += a0;
-          rs1 += a1;
-        } else {
-#pragma unroll
-          for (int e = 0; e < 32; e += 2) {
-            float ev[2];
-#pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const int64_t col = col0 + half * 64 + c * 32 + e + u;
-              const float s = __uint_as_float(v[e + u]);
-              float x = (col < args.Nb && row < args.Ma) ? ex2_approx(s * kLog2e) : 0.f;
-              if (col < args.Nb) rs0 += x;
-              if (col == drow) {       // keep the positive out of the bf16 column sum: finalize adds it in fp32
-                dval = s;
-                dfound = true;
-                x = 0.f;
+            for (int e = 0; e < 32; e += 2) {
+              float e0, e1;
+              if (e < kPoly) {
+                exp_poly2<4>(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), e0, e1);
+              } else {
+                float y0, y1;
+                unpack2(mul2(pack2(__uint_as_float(v[e]), __uint_as_float(v[e + 1])), pack2(kLog2e, kLog2e)), y0, y1);
+                e0 = ex2_approx(y0);
+                e1 = ex2_approx(y1);
               }
-              ev[u] = x;
+              acc = add2(acc, pack2(e0, e1));
+              packed[e >> 1] = bf16x2_bits(e0, e1);
             }
-            packed[e >> 1] = bf16x2_bits(ev[0], ev[1]);
-          }
-        }
-        uint8_t* panel = E + (uint32_t)half * kPanelBytes;   // column half == 64-column panel
+            float a0, a1;
+            unpack2(acc, a0, a1);
+            rs[h] += a0 + a1;
+          } else {
 #pragma unroll
-        for (int g = 0; g < 4; ++g)
-          *reinterpret_cast<uint4*>(panel + sw128_offset((uint32_t)i, (uint32_t)(c * 4 + g))) =
-              make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+            for (int e = 0; e < 32; e += 2) {
+              float ev[2];
+#pragma unroll
+              for (int u = 0; u < 2; ++u) {
+                const int64_t col = col0 + quarter * 32 + e + u;
+                const float sv = __uint_as_float(v[e + u]);
+                float x = (col < args.Nb && row < args.Ma) ? ex2_approx(sv * kLog2e) : 0.f;
+                if (col < args.Nb) rs[h] += x;
+                if (col == drow) {       // keep the positive out of the bf16 column sum: col_reduce adds it in fp32
+                  dval[h] = sv;
+                  dfound[h] = true;
+                  x = 0.f;
+                }
+                ev[u] = x;
+              }
+              packed[e >> 1] = bf16x2_bits(ev[0], ev[1]);
+            }
+          }
+          if (threadIdx.x == 64) PCLIP_TRACE(5, t * nh + h);
+          mbar_wait(&e_empty[h], ((uint32_t)t & 1u) ^ 1u);   // the column-sum MMA of item (t-1, h) has consumed E[h]
+          const uint32_t panel = e_base + (uint32_t)h * kTileBytes + (uint32_t)(quarter >> 1) * kPanelBytes;
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            st_shared_v4(panel + sw128_offset((uint32_t)i, (uint32_t)((quarter & 1) * 4 + g)), packed[4 * g],
+                         packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+          fence_proxy_async_smem();
+          mbar_arrive(&e_full[h]);
+          if (threadIdx.x == 64) PCLIP_TRACE(6, t * nh + h);
+        }
       }
-      tc_fence_before_sync();
-      mbar_arrive(&s_empty[buf]);
-      fence_proxy_async_smem();
-      mbar_arrive(&e_full[buf]);
-      if (half == 0 && t > 0) flush_cols(t - 1);   // one tile behind: never waits on the MMA just requested
+      if (quarter == 0 && t > 0) flush_cols(t - 1);   // one tile behind: never waits on the MMA just requested
     }
-    if (half == 0 && ntiles > 0) flush_cols(ntiles - 1);
-    if (row < args.Ma) {
-      args.rowpart[((int64_t)blockIdx.y * 2 + half) * args.Ma + row] = rs0 + rs1;
-      if (dfound) args.diag[row] = dval;
+    if (quarter == 0 && ntiles > 0) flush_cols(ntiles - 1);
+    // row sums: one partial per (split, column quarter)
+#pragma unroll
+    for (int h = 0; h < kH; ++h) {
+      const int64_t row = row0 + h * kTile + i;
+      if (h < nh && row < args.Ma) {
+        args.rowpart[((int64_t)blockIdx.y * 4 + quarter) * args.Ma + row] = rs[h];
+        if (dfound[h]) args.diag[row] = dval[h];
+      }
     }
   }
   tc_fence_before_sync();
@@ -604,9 +665,31 @@ static void plan2(int64_t row_blocks, int64_t ntiles, int n_sides, int max_split
   *nsplit = (int)ceil_div(ntiles, *tps);
 }
 
+// Column splits so that the CTA count fills whole waves of the SMs (one CTA per SM): 512 row blocks on 148 SMs are
+// 3.46 waves (87 % of the last wave's SM-time used); split in two they are 6.92 (99 %).
+static void plan_waves(int64_t row_blocks, int64_t ntiles, int n_sides, int max_split, int* nsplit, int* tps) {
+  const int sms = std::max(device_sm_count(), 1);
+  if (row_blocks * n_sides < sms) return plan2(row_blocks, ntiles, n_sides, 8 * max_split, nsplit, tps);
+  double best = 0.0;
+  int best_ns = 1;
+  for (int ns = 1; ns <= max_split && ns * 4 <= ntiles; ++ns) {
+    const int64_t t = ceil_div(ntiles, (int64_t)ns);                       // tiles per split
+    const int64_t ctas = row_blocks * n_sides * ceil_div(ntiles, t);
+    const double eff = (double)ctas / (double)(ceil_div(ctas, (int64_t)sms) * sms);
+    if (eff > best + 0.02) {
+      best = eff;
+      best_ns = ns;
+    }
+  }
+  *tps = (int)ceil_div(ntiles, (int64_t)best_ns);
+  *nsplit = (int)ceil_div(ntiles, (int64_t)*tps);
+}
+
 size_t tc2_grad_workspace(int64_t Ma, int64_t Nb) {
-  int ns, tps;
-  plan2(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 1, 8, &ns, &tps);
+  int ns, ns2, tps;
+  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 1, 4, &ns, &tps);
+  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 2, 4, &ns2, &tps);
+  ns = std::max(ns, ns2);
   return ns > 1 ? 2 * align_up((size_t)ns * Ma * c2::kDim * sizeof(float), 1024) + 2048 : 2048;
 }
 
@@ -624,7 +707,7 @@ int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale
   }
   const int64_t Ma = sides[0].Ma, Nb = sides[0].Nb;
   int nsplit, tps;
-  plan2(ceil_div(Ma, kRows), ceil_div(Nb, kTile), n_sides, 8, &nsplit, &tps);
+  plan_waves(ceil_div(Ma, kRows), ceil_div(Nb, kTile), n_sides, 4, &nsplit, &tps);
   Workspace w(ws, ws_bytes);
   Tc2BwdArgs args;
   CUtensorMap maps[4];
@@ -647,7 +730,7 @@ int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale
   args.gscale = gscale;
   PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc2_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmem));
   dim3 grid((unsigned)ceil_div(Ma, kRows), (unsigned)nsplit, (unsigned)n_sides);
-  tc2_grad_kernel<<<grid, kThreads, kBwdSmem, st>>>(maps[0], maps[1], maps[2], maps[3], args);
+  tc2_grad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(maps[0], maps[1], maps[2], maps[3], args);
   PCLIP_CHECK_LAUNCH();
   if (nsplit > 1) {
     for (int i = 0; i < n_sides; ++i) {
@@ -661,14 +744,14 @@ int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale
 }
 
 static void plan_fwd2(int64_t Ma, int64_t Nb, int* nsplit, int* tps) {
-  plan2(ceil_div(Ma, c2::kTile), ceil_div(Nb, c2::kTile), 1, 64, nsplit, tps);
+  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 1, 8, nsplit, tps);
 }
 
 size_t tc2_sumexp_workspace(int64_t Ma, int64_t Nb) {
   int ns, tps;
   plan_fwd2(Ma, Nb, &ns, &tps);
-  return align_up((size_t)2 * ns * Ma * sizeof(float), 1024) +
-         align_up((size_t)ceil_div(Ma, c2::kTile) * Nb * sizeof(float), 1024) + 2048;
+  return align_up((size_t)4 * ns * Ma * sizeof(float), 1024) +
+         align_up((size_t)ceil_div(Ma, c2::kRows) * Nb * sizeof(float), 1024) + 2048;
 }
 
 int tc2_sumexp(const void* a, const void* b, int64_t Ma, int64_t Nb, int64_t diag_offset, int D, float* rowsum,
@@ -677,20 +760,57 @@ int tc2_sumexp(const void* a, const void* b, int64_t Ma, int64_t Nb, int64_t dia
   PCLIP_REQUIRE(D == kDim, PCLIP_ERR_UNSUPPORTED, "bf16 tensor-core path needs D == %d (got %d)", kDim, D);
   int nsplit, tps;
   plan_fwd2(Ma, Nb, &nsplit, &tps);
-  const int nrb = (int)ceil_div(Ma, kTile);
+  const int nrb = (int)ceil_div(Ma, kRows);
   Workspace w(ws, ws_bytes);
-  float* rowpart = w.take<float>((size_t)2 * nsplit * Ma);
+  float* rowpart = w.take<float>((size_t)4 * nsplit * Ma);
   float* colpart = w.take<float>((size_t)nrb * Nb);
   PCLIP_REQUIRE(ws && w.ok(), PCLIP_ERR_WORKSPACE, "sumexp: workspace too small");
   CUtensorMap ma, mb;
   PCLIP_TRY(make_tmap_bf16_2d(&ma, a, (uint64_t)Ma, kDim, kDim, kTile, 64));
   PCLIP_TRY(make_tmap_bf16_2d(&mb, b, (uint64_t)Nb, kDim, kDim, kTile, 64));
-  Tc2FwdArgs args{Ma, Nb, diag_offset, rowpart, colpart, diag, tps};
-  PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc2_sumexp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+  static const char* trace_path = getenv("PCLIP_FWD_TRACE");
+  long long* trace = nullptr;
+  if (trace_path) {
+    PCLIP_CHECK_CUDA(cudaMalloc(&trace, 8 * kTraceItems * sizeof(long long)));
+    PCLIP_CHECK_CUDA(cudaMemsetAsync(trace, 0, 8 * kTraceItems * sizeof(long long), st));
+  }
+  Tc2FwdArgs args{Ma, Nb, diag_offset, rowpart, colpart, diag, tps, trace};
   dim3 grid((unsigned)nrb, (unsigned)nsplit);
-  tc2_sumexp_kernel<<<grid, kThreads, kFwdSmem, st>>>(ma, mb, args);
+  // exps per 32 on the FMA pipes (tuning knob; the default was chosen from B200 measurements, profiles/)
+  static const int poly = [] {
+    const char* e = getenv("PCLIP_FWD_POLY");
+    return e ? atoi(e) : kFwdPoly;
+  }();
+#define PCLIP_LAUNCH_FWD(P)                                                                                          \
+  do {                                                                                                               \
+    PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc2_sumexp_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
+                                          (int)kFwdSmem));                                                           \
+    tc2_sumexp_kernel<P><<<grid, kFwdThreads, kFwdSmem, st>>>(ma, mb, args);                                         \
+  } while (0)
+  if (poly <= 0) PCLIP_LAUNCH_FWD(0);
+  else if (poly <= 6) PCLIP_LAUNCH_FWD(6);
+  else if (poly <= 10) PCLIP_LAUNCH_FWD(10);
+  else if (poly <= 14) PCLIP_LAUNCH_FWD(14);
+  else PCLIP_LAUNCH_FWD(18);
+#undef PCLIP_LAUNCH_FWD
   PCLIP_CHECK_LAUNCH();
-  sum_partials_kernel<<<(unsigned)ceil_div(Ma, 256), 256, 0, st>>>(rowpart, 2 * nsplit, Ma, rowsum);
+  if (trace) {   // debug only: synchronises
+    static long long h[8 * kTraceItems];
+    PCLIP_CHECK_CUDA(cudaStreamSynchronize(st));
+    PCLIP_CHECK_CUDA(cudaMemcpy(h, trace, sizeof(h), cudaMemcpyDeviceToHost));
+    cudaFree(trace);
+    if (FILE* f = fopen(trace_path, "w")) {
+      long long t0 = h[1 * kTraceItems];
+      fprintf(f, "# item tma_issue s_issue c_issue epi_sfull epi_loaded epi_math_done epi_done (clocks since S(0) issue)\n");
+      for (int u = 0; u < kTraceItems; ++u) {
+        fprintf(f, "%3d", u);
+        for (int ev : {0, 1, 2, 3, 4, 5, 6}) fprintf(f, " %8lld", h[ev * kTraceItems + u] ? h[ev * kTraceItems + u] - t0 : -1);
+        fprintf(f, "\n");
+      }
+      fclose(f);
+    }
+  }
+  sum_partials_kernel<<<(unsigned)ceil_div(Ma, 256), 256, 0, st>>>(rowpart, 4 * nsplit, Ma, rowsum);
   PCLIP_CHECK_LAUNCH();
   col_reduce_kernel<<<(unsigned)ceil_div(Nb, 256), 256, 0, st>>>(colpart, nrb, Nb, diag, diag_offset, Ma, colsum);
   PCLIP_CHECK_LAUNCH();

@@ -12,6 +12,7 @@ from . import _lib as L
 
 F32 = L.COMPUTE_F32
 BF16 = L.COMPUTE_BF16
+SINGLE_PASS_MIN_COLS = 2048   # same threshold as pclip_clip_loss (csrc/api.cu)
 
 
 def default_compute() -> int:
@@ -181,9 +182,17 @@ class ClipPlan:
         self.local_is_full = Ma == Nb
         self.xf = self.xl if self.local_is_full else torch.empty(Nb, D, dtype=self.cdt, device=dev)
         self.yf = self.yl if self.local_is_full else torch.empty(Nb, D, dtype=self.cdt, device=dev)
-        self.xfT = torch.zeros(D, self.ldT, dtype=self.cdt, device=dev) if tc else None
-        self.yfT = torch.zeros(D, self.ldT, dtype=self.cdt, device=dev) if tc else None
+        # second-generation bf16 kernels: single-pass forward (row AND column sums from one sweep over S) and a
+        # gradient kernel that needs no transposed operand copies; PCLIP_CLIP_GEN=1 selects the first generation
+        # (below SINGLE_PASS_MIN_COLS columns the two-sided forward is used: its column sums are fp32-exact, whereas the
+        # single pass sums bf16-rounded exps -- errors that average out over thousands of rows but not over 16)
+        self.single_pass = tc and os.environ.get("PCLIP_CLIP_GEN", "2") != "1" and Nb >= SINGLE_PASS_MIN_COLS
+        need_T = tc and os.environ.get("PCLIP_CLIP_GEN", "2") == "1"
+        self.xfT = torch.zeros(D, self.ldT, dtype=self.cdt, device=dev) if need_T else None
+        self.yfT = torch.zeros(D, self.ldT, dtype=self.cdt, device=dev) if need_T else None
         self.rowsum, self.colsum = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
+        # single-pass: column sums of ALL Nb columns over this plan's rows (partial under row sharding)
+        self.colsum_f = self.colsum if self.local_is_full else torch.empty(Nb, **f32)
         self.diag, self.diag2 = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
         self.row_lse, self.col_lse = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
         self.rinv, self.cinv = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
@@ -194,6 +203,7 @@ class ClipPlan:
         self.dx, self.dy = torch.empty(Ma, D, **f32), torch.empty(Ma, D, **f32)
         lib = L.lib()
         n = max(lib.pclip_clip_rowsumexp_workspace_bytes(Ma, Nb, D, compute),
+                lib.pclip_clip_sumexp_workspace_bytes(Ma, Nb, D, compute) if tc else 0,
                 lib.pclip_clip_grad_workspace_bytes(Ma, Nb, D, compute), 1024)
         self.ws_bytes = int(n)
         self._ws_owner, self.ws = L.workspace(n, dev)
@@ -212,7 +222,7 @@ class ClipPlan:
 
     def transpose_full(self):
         """After an all-gather into xf / yf: the transposed copies the bf16 gradient kernel reads."""
-        if self.compute != BF16 or self.local_is_full:
+        if self.xfT is None or self.local_is_full:
             return
         lib = L.lib()
         for src, dst in ((self.xf, self.xfT), (self.yf, self.yfT)):
@@ -223,6 +233,17 @@ class ClipPlan:
             L.FwdSide(L.ptr(self.xl), L.ptr(self.yf), self.Ma, self.Nb, self.off, L.ptr(self.rowsum), L.ptr(self.diag)),
             L.FwdSide(L.ptr(self.yl), L.ptr(self.xf), self.Ma, self.Nb, self.off, L.ptr(self.colsum), L.ptr(self.diag2)))
         L.check(L.lib().pclip_clip_rowsumexp(sides, 2, self.D, self.compute, self.ws, self.ws_bytes, self._st()))
+
+    def sumexp(self):
+        """Single-pass forward: rowsum (complete), colsum_f (all Nb columns, summed over THIS plan's rows), diag."""
+        L.check(L.lib().pclip_clip_sumexp(L.ptr(self.xl), L.ptr(self.yf), self.Ma, self.Nb, self.off, self.D,
+                                          self.compute, L.ptr(self.rowsum), L.ptr(self.colsum_f), L.ptr(self.diag),
+                                          self.ws, self.ws_bytes, self._st()))
+
+    def take_local_colsum(self):
+        """After the all-reduce of colsum_f over ranks: the column sums of this rank's own positives."""
+        if not self.local_is_full:
+            self.colsum.copy_(self.colsum_f[self.off:self.off + self.Ma])
 
     def finalize(self, B_total: int):
         """loss[0] = 1/(2B) sum_i (log R_i + log C_i - 2 S_ii) over the local rows; 1/R, 1/C for the backward."""
@@ -247,7 +268,9 @@ class ClipPlan:
                 events[name][i].record(torch.cuda.current_stream(self.dev))
         assert self.local_is_full
         rec("pack", 0); self.pack(xs, ys); rec("pack", 1)
-        rec("rowsumexp", 0); self.rowsumexp(); rec("rowsumexp", 1)
+        rec("rowsumexp", 0)
+        self.sumexp() if self.single_pass else self.rowsumexp()
+        rec("rowsumexp", 1)
         self.finalize(self.Nb)
         rec("grad", 0); self.grad(self.Nb); rec("grad", 1)
         return self.loss, self.dx, self.dy

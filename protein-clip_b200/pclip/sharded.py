@@ -4,8 +4,9 @@ Rank p owns rows [p*B/P, (p+1)*B/P) of BOTH modalities.  One step:
 
   1. pack local rows to the compute dtype                                   (kernel, local)
   2. all-gather X and Y over NCCL / NVLink                                   (2 x B*D*2 bytes in bf16)
-  3. row sums  R_i = sum_j exp(x_i . y_j)  for local i against ALL y, and
-     col sums  C_i = sum_j exp(y_i . x_j)  for local i against ALL x          (kernel, local, complete)
+  3. bf16 (single pass): one sweep over X_p Y^T gives the row sums R_i of the local rows (complete) and the
+     column sums C_j of ALL columns over the local rows (partial) -> all-reduce of B floats.
+     fp32 / first generation (two-sided): R_i from (X_p, Y) and C_i from (Y_p, X), both complete locally.
   4. loss partial -> all-reduce of one float; all-gather of 1/R and 1/C       (2 x B floats)
   5. dX_local = sum_j P_ij y_j  and  dY_local = sum_j P_ji x_j               (kernel, local, complete)
 
@@ -48,7 +49,14 @@ class ShardedClip:
             dist.all_gather_into_tensor(s.xf, s.xl, group=g)
             dist.all_gather_into_tensor(s.yf, s.yl, group=g)
         s.transpose_full()
-        rec("rowsumexp", 0); s.rowsumexp(); rec("rowsumexp", 1)
+        if getattr(s, "single_pass", False):
+            # one sweep over X_p Y^T: row sums complete, column sums partial over this rank's rows
+            rec("rowsumexp", 0); s.sumexp(); rec("rowsumexp", 1)
+            if self.P > 1:
+                dist.all_reduce(s.colsum_f, group=g)
+            s.take_local_colsum()
+        else:
+            rec("rowsumexp", 0); s.rowsumexp(); rec("rowsumexp", 1)
         s.finalize(self.B)
         if self.P > 1:
             dist.all_reduce(s.loss, group=g)

@@ -4,7 +4,8 @@ import torch
 
 
 class OracleStages:
-    def __init__(self, Ma, Nb, D, diag_offset):
+    def __init__(self, Ma, Nb, D, diag_offset, single_pass=False):
+        self.single_pass = single_pass
         z = lambda *s: torch.zeros(*s, dtype=torch.float64)  # noqa: E731
         self.Ma, self.Nb, self.D, self.off, self.dev = Ma, Nb, D, diag_offset, torch.device("cpu")
         self.xl, self.yl, self.xf, self.yf = z(Ma, D), z(Ma, D), z(Nb, D), z(Nb, D)
@@ -24,6 +25,15 @@ class OracleStages:
         self.R = (self.xl @ self.yf.t()).exp().sum(1)      # ref: training_utils.py:85-87
         self.C = (self.yl @ self.xf.t()).exp().sum(1)      # :88 (column sums == row sums of the transposed side)
         self.diag = (self.xl * self.yf[self.off:self.off + self.Ma]).sum(-1)
+
+    def sumexp(self):
+        e = (self.xl @ self.yf.t()).exp()
+        self.R = e.sum(1)
+        self.colsum_f = e.sum(0)                             # partial over this rank's rows
+        self.diag = (self.xl * self.yf[self.off:self.off + self.Ma]).sum(-1)
+
+    def take_local_colsum(self):
+        self.C = self.colsum_f[self.off:self.off + self.Ma].clone()
 
     def finalize(self, B):
         self.loss[0] = (self.R.log() + self.C.log() - 2 * self.diag).sum() / (2 * B)

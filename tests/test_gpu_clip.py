@@ -141,6 +141,29 @@ def test_clip_multi_tile_vs_oracle(ops, mode, B):
     assert_close(dy, dy_o, tol * 3, "dy")
 
 
+@pytest.mark.parametrize("Ma,Nb,off", [(16, 16, 0), (129, 129, 0), (256, 256, 0), (257, 257, 0), (1000, 1000, 0),
+                                       (4096, 4096, 0), (8256, 8256, 0), (512, 2048, 512), (300, 1200, 900),
+                                       (2048, 16384, 6144)])
+def test_single_pass_sumexp_vs_oracle(ops, Ma, Nb, off):
+    """pclip_clip_sumexp (one sweep over S: row sums, column sums, diagonal; ref: training_utils.py:85-88) on square,
+    ragged and row-sharded (Ma < Nb, diag_offset) shapes against float64 on the same bf16-rounded operands.  Row sums
+    are fp32 sums of fp32 exps; column sums are fp32 sums of bf16-rounded exps (relative error <= 2^-9 per term)."""
+    from pclip import synth
+    x, y = synth.clip_scaled_embeddings(Nb, 128, cfg_id=Nb + 7, trained_like=(Nb % 3 == 0))
+    xb, yb = x.bfloat16().cuda(), y.bfloat16().cuda()
+    plan = ops.ClipPlan(Ma, Nb, 128, ops.BF16, "cuda", diag_offset=off)
+    plan.xl.copy_(xb[off:off + Ma]); plan.yl.copy_(yb[off:off + Ma])
+    if not plan.local_is_full:
+        plan.xf.copy_(xb); plan.yf.copy_(yb)
+    plan.sumexp()
+    s = xb[off:off + Ma].double() @ yb.double().t()
+    e = s.exp()
+    idx = torch.arange(Ma, device="cuda")
+    assert float(((plan.rowsum.double() - e.sum(1)) / e.sum(1)).abs().max()) < 2e-5
+    assert float(((plan.colsum_f.double() - e.sum(0)) / e.sum(0)).abs().max()) < 2.0 ** -9
+    assert float((plan.diag.double() - s[idx, idx + off]).abs().max()) < 1e-5
+
+
 def test_clip_full_size_properties(ops):
     """cfg 4 (B = 65 536, bf16): size-independent properties instead of an O(B^2) oracle pass.
     (a) all-zero embeddings: every logit is 0, so loss = ln B and both gradients vanish;

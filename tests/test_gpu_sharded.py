@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("mode", ["f32", "bf16"])
-@pytest.mark.parametrize("P,B", [(2, 512), (4, 1024), (8, 2048)])
+@pytest.mark.parametrize("P,B", [(2, 512), (4, 1024), (8, 2048), (4, 4096)])
 def test_emulated_ranks_match_single_gpu(P, B, mode):
     from pclip import ops, synth
     compute = ops.F32 if mode == "f32" else ops.BF16
@@ -25,7 +25,17 @@ def test_emulated_ranks_match_single_gpu(P, B, mode):
         p.xf.copy_(xf)
         p.yf.copy_(yf)
         p.transpose_full()
-        p.rowsumexp()
+    if plans[0].single_pass:       # pclip/sharded.py: one sweep per rank, column sums all-reduced over ranks
+        for p in plans:
+            p.sumexp()
+        colsum = sum(p.colsum_f.clone() for p in plans)                              # the all-reduce of B floats
+        for p in plans:
+            p.colsum_f.copy_(colsum)
+            p.take_local_colsum()
+    else:
+        for p in plans:
+            p.rowsumexp()
+    for p in plans:
         p.finalize(B)
     loss = sum(p.loss.clone() for p in plans)                                        # the all-reduce
     rinv, cinv = torch.cat([p.rinv for p in plans]), torch.cat([p.cinv for p in plans])

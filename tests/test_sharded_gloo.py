@@ -12,7 +12,7 @@ import torch.multiprocessing as mp
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, B, ret):
+def _worker(rank, world, port, B, single_pass, ret):
     for p in (REPO, os.path.join(REPO, "protein-clip_b200"), os.path.join(REPO, "tests")):
         if p not in sys.path:
             sys.path.insert(0, p)
@@ -24,7 +24,7 @@ def _worker(rank, world, port, B, ret):
         from pclip import sharded, synth
         x, y = synth.clip_scaled_embeddings(B, 128, cfg_id=11, trained_like=True)
         Ma = B // world
-        job = sharded.ShardedClip(B, 128, 0, "cpu", stages=OracleStages(Ma, B, 128, rank * Ma))
+        job = sharded.ShardedClip(B, 128, 0, "cpu", stages=OracleStages(Ma, B, 128, rank * Ma, single_pass=single_pass))
         sl = slice(rank * Ma, (rank + 1) * Ma)
         # two uneven chunks per rank, like GradCache leaves
         cut = Ma // 3
@@ -38,12 +38,13 @@ def _worker(rank, world, port, B, ret):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("single_pass", [False, True], ids=["two_sided", "single_pass"])
 @pytest.mark.parametrize("world,B", [(2, 64), (3, 96)])
-def test_row_sharded_clip_matches_unsharded(world, B):
+def test_row_sharded_clip_matches_unsharded(world, B, single_pass):
     ctx = mp.get_context("spawn")
     ret = ctx.Manager().dict()
-    port = 29600 + world + (os.getpid() % 200)
-    procs = [ctx.Process(target=_worker, args=(r, world, port, B, ret)) for r in range(world)]
+    port = 29600 + world + 10 * int(single_pass) + (os.getpid() % 200)
+    procs = [ctx.Process(target=_worker, args=(r, world, port, B, single_pass, ret)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
