@@ -115,6 +115,15 @@ __device__ __forceinline__ uint32_t bf16x2_bits(float lo, float hi) {
 // =================================================================================================================
 // gradient: da_i = scale * ( sum_j exp(a_i . b_j) (rinv_i + cinv_j) b_j  -  2 b_(off + i) )
 // =================================================================================================================
+// debug timeline (PCLIP_FWD_TRACE / PCLIP_BWD_TRACE = file): SM clocks of pipeline events of CTA (0,0,0)
+namespace c2 {
+constexpr int kTraceItems = 96;
+}
+#define PCLIP_TRACE(ev, u)                                                                       \
+  do {                                                                                          \
+    if (tr && (u) < kTraceItems) tr[(ev) * kTraceItems + (u)] = clock64();                      \
+  } while (0)
+
 struct Tc2BwdSide {
   int64_t Ma, Nb, diag_offset;
   const float* rinv;
@@ -128,6 +137,7 @@ struct Tc2BwdArgs {
   int direct;
   float scale;
   const float* gscale;
+  long long* trace;
 };
 
 namespace c2 {
@@ -169,9 +179,11 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
   uint64_t* s_full = y_empty + kBwdStages;    // [kH]
   uint64_t* p_full = s_full + kH;             // [kH]
   uint64_t* d_full = p_full + kH;             // 1
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_full + 1);
+  uint64_t* pv_done = d_full + 1;             // [kH]: the P . Y MMA of the previous tile has finished reading P_h
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + kH);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  long long* tr = (args.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? args.trace : nullptr;
   if (threadIdx.x == 0) {
     mbar_init(a_full, 1);
     for (int i = 0; i < kBwdStages; ++i) {
@@ -181,6 +193,7 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
     for (int i = 0; i < kH; ++i) {
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 256);
+      mbar_init(&pv_done[i], 1);
     }
     mbar_init(d_full, 1);
     fence_mbar_init();
@@ -219,6 +232,7 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
       auto issue_s = [&](int h, int t) {
         const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kBwdStages) * kTileBytes);
         const uint32_t a_addr = smem_u32(a_tiles + h * kTileBytes);
+        PCLIP_TRACE(0, 2 * t + h);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
           umma_bf16_ss(tmem_base + (uint32_t)h * kTile, kmajor_desc(a_addr, k), kmajor_desc(y_addr, k), idesc_s,
@@ -233,11 +247,8 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         for (int h = 0; h < nh; ++h) {
           mbar_wait(&p_full[h], (uint32_t)t & 1u);        // P_h(t) written => S_h(t) fully consumed
           tc_fence_after_sync();
-          const uint32_t p_addr = smem_u32(p_tiles + h * kTileBytes);
-#pragma unroll
-          for (int k = 0; k < 8; ++k)
-            umma_bf16_ss(tmem_base + (uint32_t)(kH + h) * kTile, kmajor_desc(p_addr, k), mnmajor_desc(y_addr, k), idesc_g,
-                         (t > 0 || k > 0) ? 1u : 0u);
+          // the next score tile of this half goes FIRST: its epilogue is the critical path (epilogue -> P.Y -> S ->
+          // epilogue was one serial chain per half, r01c profile); P_h stays protected by pv_done[h]
           if (t + 1 < ntiles) {
             if (h == 0) {
               const int st = (t + 1) % kBwdStages;
@@ -246,6 +257,13 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
             }
             issue_s(h, t + 1);
           }
+          const uint32_t p_addr = smem_u32(p_tiles + h * kTileBytes);
+          PCLIP_TRACE(1, 2 * t + h);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_bf16_ss(tmem_base + (uint32_t)(kH + h) * kTile, kmajor_desc(p_addr, k), mnmajor_desc(y_addr, k), idesc_g,
+                         (t > 0 || k > 0) ? 1u : 0u);
+          umma_commit(&pv_done[h]);
         }
         umma_commit(&y_empty[t % kBwdStages]);
       }
@@ -266,9 +284,12 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
         float* cs = cinv_s + (t & 1) * kTile;
         if (ch == 0) cs[i] = (col0 + i < sd.Nb) ? sd.cinv[col0 + i] : 0.f;   // 0 also masks the zero-filled columns beyond Nb
+        const bool tracer = (threadIdx.x & 255) == 64;   // first thread of each half's first warp
+        if (tracer) PCLIP_TRACE(2, 2 * t + h);
         named_bar_sync(1 + h, 256);
         mbar_wait(&s_full[h], (uint32_t)t & 1u);
         tc_fence_after_sync();
+        if (tracer) PCLIP_TRACE(3, 2 * t + h);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t v[32];
@@ -291,6 +312,9 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
             unpack2(mul2(pack2(e0, e1), w), p0, p1);
             packed[e >> 1] = bf16x2_bits(p0, p1);
           }
+          if (c == 0 && tracer) PCLIP_TRACE(4, 2 * t + h);
+          if (c == 0 && t > 0) mbar_wait(&pv_done[h], (uint32_t)(t - 1) & 1u);   // P_h(t-1) has been consumed
+          if (c == 0 && tracer) PCLIP_TRACE(5, 2 * t + h);
 #pragma unroll
           for (int g = 0; g < 4; ++g)
             st_shared_v4(p_addr + sw128_offset((uint32_t)i, (uint32_t)(c * 4 + g)), packed[4 * g], packed[4 * g + 1],
@@ -299,6 +323,7 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         tc_fence_before_sync();
         fence_proxy_async_smem();
         mbar_arrive(&p_full[h]);
+        if (tracer) PCLIP_TRACE(6, 2 * t + h);
       }
       if (ntiles > 0) {
         mbar_wait(d_full, 0);
@@ -355,6 +380,237 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
 }
 
 // =================================================================================================================
+// gradient, transposed formulation (third generation): both contractions are issued with N = 256.
+//   S^T [128 cols j x 256 rows i] = Y_t . A^T          (A = column tile, K-major;  B = the CTA's 256 rows, K-major)
+//   dA^T[128 d      x 256 rows i] += Y_t^T . P^T        (A = column tile read MN-major; B = P^T [j][i], MN-major)
+// Why: a tcgen05.mma with both operands in shared memory is paced by the operand read (~96 B/clk): M128 N128 K16 takes
+// 86 clk, N256 takes 128 clk (tools/probe_mma.cu), i.e. N = 256 is the only shape that runs at the tensor-pipe rate,
+// and it halves the SMEM operand traffic per score.  The epilogue thread owns one COLUMN j (TMEM lane): 1/C_j lives in
+// a register, 1/R_i of the 256 rows is staged in SMEM once per CTA.  S^T has one accumulator (TMEM is full with dA^T):
+// it is released as soon as the epilogue holds the scores in registers, so S^T(t+1) runs under the epilogue of tile t.
+// =================================================================================================================
+namespace c3 {
+using namespace c2;
+constexpr int kStages = 3;
+constexpr int kEpiWarps = 16;
+constexpr int kThreads3 = 64 + 32 * kEpiWarps;
+constexpr uint32_t kABytes = kRows * kDim * 2;       // 64 KB, panel-major: [2 panels][256 rows][64 d]
+constexpr uint32_t kPBytes = kTile * kRows * 2;      // 64 KB: [4 panels of 64 rows i][128 j][64 i]
+// A | Y ring | P^T | rinv staging [256] | barriers
+constexpr uint32_t kSmem3 = kABytes + kStages * kTileBytes + kPBytes + kRows * 4 + 256 + 768;
+static_assert(kSmem3 <= 232448, "shared memory budget");
+}  // namespace c3
+
+__global__ void __launch_bounds__(c3::kThreads3, 1)
+tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__ CUtensorMap tb0,
+                const __grid_constant__ CUtensorMap ta1, const __grid_constant__ CUtensorMap tb1,
+                const Tc2BwdArgs args) {
+  using namespace c3;
+  const Tc2BwdSide& sd = args.s[blockIdx.z];
+  const CUtensorMap* ta = blockIdx.z == 0 ? &ta0 : &ta1;
+  const CUtensorMap* tb = blockIdx.z == 0 ? &tb0 : &tb1;
+  const int64_t row0 = (int64_t)blockIdx.x * kRows;
+  if (row0 >= sd.Ma) return;
+  const int ntiles_all = (int)((sd.Nb + kTile - 1) / kTile);
+  const int tile_begin = blockIdx.y * args.tiles_per_split;
+  const int ntiles = max(min(tile_begin + args.tiles_per_split, ntiles_all) - tile_begin, 0);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_rows = smem;
+  uint8_t* y_tiles = a_rows + kABytes;
+  uint8_t* p_t = y_tiles + kStages * kTileBytes;
+  float* rinv_s = reinterpret_cast<float*>(p_t + kPBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rinv_s + kRows);
+  uint64_t* a_full = bars;                 // 1
+  uint64_t* y_full = a_full + 1;           // kStages
+  uint64_t* y_empty = y_full + kStages;    // kStages
+  uint64_t* s_full = y_empty + kStages;    // 1: S^T(t) is in TMEM
+  uint64_t* s_free = s_full + 1;           // 1: every epilogue thread holds its scores of tile t in registers
+  uint64_t* p_full = s_free + 1;           // 1: P^T(t) is in SMEM
+  uint64_t* pv_done = p_full + 1;          // 1: the second MMA has consumed P^T(t)
+  uint64_t* d_full = pv_done + 1;          // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_full + 1);
+  if (threadIdx.x == 0 && reinterpret_cast<uint8_t*>(tmem_slot + 1) > smem_raw + kSmem3) __trap();  // alignment slack
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  long long* tr = (args.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? args.trace : nullptr;
+  if (threadIdx.x == 0) {
+    mbar_init(a_full, 1);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&y_full[i], 1);
+      mbar_init(&y_empty[i], 1);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(s_free, 32 * kEpiWarps);
+    mbar_init(p_full, 32 * kEpiWarps);
+    mbar_init(pv_done, 1);
+    mbar_init(d_full, 1);
+    fence_mbar_init();
+  }
+  if (threadIdx.x < kRows) {
+    const int64_t r = row0 + threadIdx.x;
+    rinv_s[threadIdx.x] = r < sd.Ma ? sd.rinv[r] : 0.f;
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_s = *tmem_slot;            // columns [0, 256): S^T; [256, 512): dA^T
+  const uint32_t tmem_d = tmem_s + kRows;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(ta);
+      tma_prefetch_desc(tb);
+      mbar_arrive_expect_tx(a_full, kABytes);    // rows beyond Ma are zero-filled by TMA (the bytes still count)
+      for (int p = 0; p < 2; ++p)
+        for (int h = 0; h < kH; ++h)
+          tma_load_2d(a_rows + p * (kABytes / 2) + h * kPanelBytes, ta, a_full, p * 64, (int32_t)(row0 + h * kTile));
+      for (int t = 0; t < ntiles; ++t) {
+        const int stage = t % kStages;
+        mbar_wait(&y_empty[stage], ((uint32_t)(t / kStages) & 1u) ^ 1u);
+        mbar_arrive_expect_tx(&y_full[stage], kTileBytes);
+        const int32_t col0 = (tile_begin + t) * kTile;
+        uint8_t* dst = y_tiles + (size_t)stage * kTileBytes;
+        tma_load_2d(dst, tb, &y_full[stage], 0, col0);
+        tma_load_2d(dst + kPanelBytes, tb, &y_full[stage], 64, col0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && ntiles > 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kRows, 0, 0);   // S^T = Y . A^T      (both K-major)
+      constexpr uint32_t idesc_g = make_idesc_bf16(kTile, kRows, 1, 1);   // dA^T += Y^T . P^T  (both MN-major)
+      const uint32_t a_addr = smem_u32(a_rows), p_addr = smem_u32(p_t);
+      mbar_wait(a_full, 0);
+      auto issue_s = [&](int t) {
+        const int stage = t % kStages;
+        mbar_wait(&y_full[stage], (uint32_t)(t / kStages) & 1u);
+        if (t > 0) mbar_wait(s_free, (uint32_t)(t - 1) & 1u);
+        tc_fence_after_sync();
+        PCLIP_TRACE(0, t);
+        const uint32_t y_addr = smem_u32(y_tiles + (size_t)stage * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_bf16_ss(tmem_s, kmajor_desc(y_addr, k),
+                       make_smem_desc_sw128(a_addr + (uint32_t)(k >> 2) * (kABytes / 2) + (uint32_t)(k & 3) * 32u, 16, 1024),
+                       idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(s_full);
+      };
+      issue_s(0);
+      for (int t = 0; t < ntiles; ++t) {
+        if (t + 1 < ntiles) issue_s(t + 1);
+        mbar_wait(p_full, (uint32_t)t & 1u);
+        tc_fence_after_sync();
+        PCLIP_TRACE(1, t);
+        const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kStages) * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_bf16_ss(tmem_d, mnmajor_desc(y_addr, k), mnmajor_desc(p_addr, k), idesc_g, (t > 0 || k > 0) ? 1u : 0u);
+        umma_commit(pv_done);
+        umma_commit(&y_empty[t % kStages]);
+      }
+      umma_commit(d_full);
+    }
+  } else {
+    // 16 epilogue warps: lane quadrant q (columns j of the tile) x row group g (64 rows i each)
+    const int g = (warp - 2) >> 2, q = warp & 3;
+    const int j = q * 32 + lane;                         // my column inside the tile == my TMEM lane
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    const uint32_t p_row = smem_u32(p_t) + (uint32_t)g * kPanelBytes;   // panel g holds rows i in [64 g, 64 g + 64)
+    const bool tracer = threadIdx.x == 64;
+    float cinv = (int64_t)tile_begin * kTile + j < sd.Nb && ntiles > 0 ? sd.cinv[(int64_t)tile_begin * kTile + j] : 0.f;
+    for (int t = 0; t < ntiles; ++t) {
+      const uint64_t cinv2 = pack2(cinv, cinv);
+      const int64_t jn = (int64_t)(tile_begin + t + 1) * kTile + j;       // prefetch the next tile's 1/C_j
+      const float cinv_next = (t + 1 < ntiles && jn < sd.Nb) ? sd.cinv[jn] : 0.f;
+      mbar_wait(s_full, (uint32_t)t & 1u);
+      tc_fence_after_sync();
+      if (tracer) PCLIP_TRACE(2, t);
+      uint32_t packed[2][16];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_s + lane_base + (uint32_t)(g * 64 + c * 32), v);
+        tmem_ld_wait();
+        if (c == 1) {                          // all my scores are in registers: S^T(t+1) may overwrite the accumulator
+          tc_fence_before_sync();
+          mbar_arrive(s_free);
+          if (tracer) PCLIP_TRACE(3, t);
+        }
+        const float* rs = rinv_s + g * 64 + c * 32;
+#pragma unroll
+        for (int e = 0; e < 32; e += 2) {
+          float e0, e1;
+          if (e < kPolyPerChunk) {
+            exp_poly2<3>(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), e0, e1);
+          } else {
+            float y0, y1;
+            unpack2(mul2(pack2(__uint_as_float(v[e]), __uint_as_float(v[e + 1])), pack2(kLog2e, kLog2e)), y0, y1);
+            e0 = ex2_approx(y0);
+            e1 = ex2_approx(y1);
+          }
+          const uint64_t w = add2(cinv2, *reinterpret_cast<const uint64_t*>(&rs[e]));
+          float p0, p1;
+          unpack2(mul2(pack2(e0, e1), w), p0, p1);
+          packed[c][e >> 1] = bf16x2_bits(p0, p1);
+        }
+      }
+      if (tracer) PCLIP_TRACE(4, t);
+      if (t > 0) mbar_wait(pv_done, (uint32_t)(t - 1) & 1u);   // P^T(t-1) has been consumed by the second MMA
+      if (tracer) PCLIP_TRACE(5, t);
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int gg = 0; gg < 4; ++gg)
+          st_shared_v4(p_row + sw128_offset((uint32_t)j, (uint32_t)(c * 4 + gg)), packed[c][4 * gg], packed[c][4 * gg + 1],
+                       packed[c][4 * gg + 2], packed[c][4 * gg + 3]);
+      fence_proxy_async_smem();
+      mbar_arrive(p_full);
+      if (tracer) PCLIP_TRACE(6, t);
+      cinv = cinv_next;
+    }
+    if (ntiles > 0) {
+      mbar_wait(d_full, 0);
+      tc_fence_after_sync();
+    }
+    // ---- final: dA^T accumulator (lane = d, column = row i) -> global; a warp store covers 32 consecutive d ----
+    const float s = args.scale * (args.gscale ? args.gscale[0] : 1.0f);
+    const int d = j;
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      uint32_t r[32];
+      if (ntiles > 0) {
+        tmem_ld_32x32b_x32(tmem_d + lane_base + (uint32_t)(g * 64 + c * 32), r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) r[e] = 0u;
+      }
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        const int64_t row = row0 + g * 64 + c * 32 + e;
+        if (row < sd.Ma) {
+          if (args.direct) {
+            const float bpos = __bfloat162float(sd.b[(sd.diag_offset + row) * kDim + d]);
+            sd.out[row * kDim + d] = s * (__uint_as_float(r[e]) - 2.0f * bpos);
+          } else {
+            sd.out[((int64_t)blockIdx.y * sd.Ma + row) * kDim + d] = __uint_as_float(r[e]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    __syncwarp();
+    tmem_dealloc<512>(tmem_s);
+  }
+}
+
+// =================================================================================================================
 // single-pass sum-exp: rowsum_i = sum_j exp(a_i . b_j) (fp32 exps), colsum_j = sum_{i != pos(j)} bf16(exp(a_i . b_j))
 // over THIS launch's rows (the diagonal term is added back in fp32 by col_reduce_kernel), diag_i = a_i . b_(off+i).
 //
@@ -376,7 +632,6 @@ struct Tc2FwdArgs {
 };
 
 namespace c2 {
-constexpr int kTraceItems = 96;
 constexpr int kFwdStages = 3;
 constexpr int kSBuf = 3;                    // score accumulators in TMEM
 constexpr uint32_t kOnesBytes = 2048;       // B operand of the column-sum MMA: [16 x 64] bf16 ones (one K panel, reused)
@@ -387,11 +642,6 @@ constexpr int kFwdPoly = PCLIP_FWD_POLY;  // of every 32 exps, this many on the 
 constexpr int kFwdEpiWarps = 16;          // 4 warps per SM sub-partition
 constexpr int kFwdThreads = 64 + 32 * kFwdEpiWarps;
 }  // namespace c2
-
-#define PCLIP_TRACE(ev, u)                                                                       \
-  do {                                                                                          \
-    if (tr && (u) < kTraceItems) tr[(ev) * kTraceItems + (u)] = clock64();                      \
-  } while (0)
 
 template <int kPoly>
 __global__ void __launch_bounds__(c2::kFwdThreads, 1)
@@ -728,10 +978,42 @@ int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale
   args.direct = nsplit == 1;
   args.scale = scale;
   args.gscale = gscale;
-  PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc2_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmem));
+  static const char* trace_path = getenv("PCLIP_BWD_TRACE");
+  args.trace = nullptr;
+  if (trace_path) {
+    PCLIP_CHECK_CUDA(cudaMalloc(&args.trace, 8 * kTraceItems * sizeof(long long)));
+    PCLIP_CHECK_CUDA(cudaMemsetAsync(args.trace, 0, 8 * kTraceItems * sizeof(long long), st));
+  }
   dim3 grid((unsigned)ceil_div(Ma, kRows), (unsigned)nsplit, (unsigned)n_sides);
-  tc2_grad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(maps[0], maps[1], maps[2], maps[3], args);
+  // PCLIP_GRAD_FORM=rows selects the row-major formulation (N = 128 MMAs, kept for A/B runs); default: transposed
+  static const bool transposed = [] {
+    const char* e = getenv("PCLIP_GRAD_FORM");
+    return !(e && e[0] == 'r');
+  }();
+  if (transposed) {
+    PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc3_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c3::kSmem3));
+    tc3_grad_kernel<<<grid, c3::kThreads3, c3::kSmem3, st>>>(maps[0], maps[1], maps[2], maps[3], args);
+  } else {
+    PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc2_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmem));
+    tc2_grad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(maps[0], maps[1], maps[2], maps[3], args);
+  }
   PCLIP_CHECK_LAUNCH();
+  if (args.trace) {   // debug only: synchronises
+    static long long h[8 * kTraceItems];
+    PCLIP_CHECK_CUDA(cudaStreamSynchronize(st));
+    PCLIP_CHECK_CUDA(cudaMemcpy(h, args.trace, sizeof(h), cudaMemcpyDeviceToHost));
+    cudaFree(args.trace);
+    if (FILE* f = fopen(trace_path, "w")) {
+      const long long t0 = h[0];
+      fprintf(f, "# item(2t+h) s_issue pv_issue epi_start epi_sfull epi_chunk0_math pvdone_passed epi_done (clocks since S(0,0))\n");
+      for (int u = 0; u < kTraceItems; ++u) {
+        fprintf(f, "%3d", u);
+        for (int ev = 0; ev < 7; ++ev) fprintf(f, " %8lld", h[ev * kTraceItems + u] ? h[ev * kTraceItems + u] - t0 : -1);
+        fprintf(f, "\n");
+      }
+      fclose(f);
+    }
+  }
   if (nsplit > 1) {
     for (int i = 0; i < n_sides; ++i) {
       grad_reduce_kernel<<<(unsigned)ceil_div(Ma * (kDim / 4), 256), 256, 0, st>>>(
