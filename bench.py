@@ -212,7 +212,7 @@ class ClipLarge:
         Ma, B, D = self.Ma, self.B, self.D
         flops = 4.0 * Ma * B * D                         # dX and dY GEMMs of this rank's rows (algorithmic)
         ach = flops / (out["grad"] * 1e-3) / 1e12
-        return {"bound": "tensor", "kernel": "tc2_grad_kernel", "achieved": round(ach, 1), "peak": peaks["tc"],
+        return {"bound": "tensor", "kernel": "tc3_grad_kernel", "achieved": round(ach, 1), "peak": peaks["tc"],
                 "unit": "TFLOP/s", "frac": round(ach / peaks["tc"], 4), "traffic": None,
                 "peak_source": f"{peaks['src']} bf16_tflops_sustained",
                 "algorithmic_flops_per_launch": flops, "kernel_ms": round(out["grad"], 4),

@@ -389,6 +389,9 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
 // a register, 1/R_i of the 256 rows is staged in SMEM once per CTA.  S^T has one accumulator (TMEM is full with dA^T):
 // it is released as soon as the epilogue holds the scores in registers, so S^T(t+1) runs under the epilogue of tile t.
 // =================================================================================================================
+#ifndef PCLIP_RINV_LD
+#define PCLIP_RINV_LD 128
+#endif
 namespace c3 {
 using namespace c2;
 constexpr int kStages = 3;
@@ -538,7 +541,16 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
           mbar_arrive(s_free);
           if (tracer) PCLIP_TRACE(3, t);
         }
-        const float* rs = rinv_s + g * 64 + c * 32;
+        // explicit shared-space loads: through a generic pointer these were LD.E.128 at 6.3 wavefronts each (r01c)
+        const uint32_t rs_addr = smem_u32(rinv_s + g * 64 + c * 32);
+        uint64_t rs2[16];
+#pragma unroll
+        for (int e = 0; e < 32; e += PCLIP_RINV_LD / 32) {
+          if (PCLIP_RINV_LD == 128)
+            asm("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(rs2[e >> 1]), "=l"(rs2[(e >> 1) + 1]) : "r"(rs_addr + 4u * e));
+          else
+            asm("ld.shared.b64 %0, [%1];" : "=l"(rs2[e >> 1]) : "r"(rs_addr + 4u * e));
+        }
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
           float e0, e1;
@@ -550,7 +562,7 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
             e0 = ex2_approx(y0);
             e1 = ex2_approx(y1);
           }
-          const uint64_t w = add2(cinv2, *reinterpret_cast<const uint64_t*>(&rs[e]));
+          const uint64_t w = add2(cinv2, rs2[e >> 1]);
           float p0, p1;
           unpack2(mul2(pack2(e0, e1), w), p0, p1);
           packed[c][e >> 1] = bf16x2_bits(p0, p1);
