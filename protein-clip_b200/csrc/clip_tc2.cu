@@ -37,18 +37,20 @@ constexpr int kThreads = 64 + 32 * 4 * kH;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kMagic = 12582912.0f;  // 1.5 * 2^23: (x + kMagic) holds round(x) in its low mantissa bits
 
+// Operand descriptors are built once per tile (`*_base`) and advanced per k-step by a constant (`*_step`).
 // K-major operand ([rows][64 bf16] panels): k-step k covers 16 bf16 = 32 B inside a 128 B swizzled row.
-__device__ __forceinline__ uint64_t kmajor_desc(uint32_t tile_addr, int k) {
-  return make_smem_desc_sw128(tile_addr + (uint32_t)(k >> 2) * kPanelBytes + (uint32_t)(k & 3) * 32u, 16, 1024);
+__device__ __forceinline__ uint64_t kmajor_base(uint32_t tile_addr) { return make_smem_desc_sw128(tile_addr, 16, 1024); }
+__device__ __forceinline__ uint64_t kmajor_step(uint64_t base, int k) {
+  return desc_advance(base, (uint32_t)(k >> 2) * kPanelBytes + (uint32_t)(k & 3) * 32u);
 }
 // The same tile read as an MN-major operand (MN runs along the 128 B rows, K along the tile's rows): k-step k covers
 // tile rows [16k, 16k+16) = two 8-row swizzle atoms (SBO = 1024 B); the two 64-element MN halves are the two panels
 // (LBO = kPanelBytes).
-__device__ __forceinline__ uint64_t mnmajor_desc(uint32_t tile_addr, int k) {
-  return make_smem_desc_sw128(tile_addr + (uint32_t)k * 2048u, kPanelBytes, 1024);
+__device__ __forceinline__ uint64_t mnmajor_base(uint32_t tile_addr) {
+  return make_smem_desc_sw128(tile_addr, kPanelBytes, 1024);
 }
+__device__ __forceinline__ uint64_t mnmajor_step(uint64_t base, int k) { return desc_advance(base, (uint32_t)k * 2048u); }
 
-// ---- packed f32x2 helpers (FFMA2 / FADD2 / FMUL2 on sm_100) ----
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
@@ -233,10 +235,10 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kBwdStages) * kTileBytes);
         const uint32_t a_addr = smem_u32(a_tiles + h * kTileBytes);
         PCLIP_TRACE(0, 2 * t + h);
+        const uint64_t ad = kmajor_base(a_addr), yd = kmajor_base(y_addr);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          umma_bf16_ss(tmem_base + (uint32_t)h * kTile, kmajor_desc(a_addr, k), kmajor_desc(y_addr, k), idesc_s,
-                       k > 0 ? 1u : 0u);
+          umma_bf16_ss(tmem_base + (uint32_t)h * kTile, kmajor_step(ad, k), kmajor_step(yd, k), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(&s_full[h]);
       };
       mbar_wait(&y_full[0], 0);
@@ -259,9 +261,10 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
           }
           const uint32_t p_addr = smem_u32(p_tiles + h * kTileBytes);
           PCLIP_TRACE(1, 2 * t + h);
+          const uint64_t pd = kmajor_base(p_addr), yd = mnmajor_base(y_addr);
 #pragma unroll
           for (int k = 0; k < 8; ++k)
-            umma_bf16_ss(tmem_base + (uint32_t)(kH + h) * kTile, kmajor_desc(p_addr, k), mnmajor_desc(y_addr, k), idesc_g,
+            umma_bf16_ss(tmem_base + (uint32_t)(kH + h) * kTile, kmajor_step(pd, k), mnmajor_step(yd, k), idesc_g,
                          (t > 0 || k > 0) ? 1u : 0u);
           umma_commit(&pv_done[h]);
         }
@@ -484,7 +487,7 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
     if (lane == 0 && ntiles > 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kRows, 0, 0);   // S^T = Y . A^T      (both K-major)
       constexpr uint32_t idesc_g = make_idesc_bf16(kTile, kRows, 1, 1);   // dA^T += Y^T . P^T  (both MN-major)
-      const uint32_t a_addr = smem_u32(a_rows), p_addr = smem_u32(p_t);
+      const uint64_t ad = kmajor_base(smem_u32(a_rows)), pd = mnmajor_base(smem_u32(p_t));
       mbar_wait(a_full, 0);
       auto issue_s = [&](int t) {
         const int stage = t % kStages;
@@ -492,11 +495,10 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         if (t > 0) mbar_wait(s_free, (uint32_t)(t - 1) & 1u);
         tc_fence_after_sync();
         PCLIP_TRACE(0, t);
-        const uint32_t y_addr = smem_u32(y_tiles + (size_t)stage * kTileBytes);
+        const uint64_t yd = kmajor_base(smem_u32(y_tiles + (size_t)stage * kTileBytes));
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          umma_bf16_ss(tmem_s, kmajor_desc(y_addr, k),
-                       make_smem_desc_sw128(a_addr + (uint32_t)(k >> 2) * (kABytes / 2) + (uint32_t)(k & 3) * 32u, 16, 1024),
+          umma_bf16_ss(tmem_s, kmajor_step(yd, k), desc_advance(ad, (uint32_t)(k >> 2) * (kABytes / 2) + (uint32_t)(k & 3) * 32u),
                        idesc_s, k > 0 ? 1u : 0u);
         umma_commit(s_full);
       };
@@ -506,10 +508,10 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         mbar_wait(p_full, (uint32_t)t & 1u);
         tc_fence_after_sync();
         PCLIP_TRACE(1, t);
-        const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kStages) * kTileBytes);
+        const uint64_t yd = mnmajor_base(smem_u32(y_tiles + (size_t)(t % kStages) * kTileBytes));
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          umma_bf16_ss(tmem_d, mnmajor_desc(y_addr, k), mnmajor_desc(p_addr, k), idesc_g, (t > 0 || k > 0) ? 1u : 0u);
+          umma_bf16_ss(tmem_d, mnmajor_step(yd, k), mnmajor_step(pd, k), idesc_g, (t > 0 || k > 0) ? 1u : 0u);
         umma_commit(pv_done);
         umma_commit(&y_empty[t % kStages]);
       }
@@ -643,12 +645,17 @@ struct Tc2FwdArgs {
   long long* trace; // debug timeline of CTA (0,0): [8][kTraceItems] SM clocks, or NULL (PCLIP_FWD_TRACE=file)
 };
 
+#ifndef PCLIP_FWD_STAGES
+#define PCLIP_FWD_STAGES 2
+#define PCLIP_FWD_EBUF 3
+#endif
 namespace c2 {
-constexpr int kFwdStages = 3;
+constexpr int kFwdStages = PCLIP_FWD_STAGES;   // column-tile ring
+constexpr int kEBuf = PCLIP_FWD_EBUF;          // bf16 exp tiles awaiting their column-sum MMA, indexed by item % kEBuf
 constexpr int kSBuf = 3;                    // score accumulators in TMEM
 constexpr uint32_t kOnesBytes = 2048;       // B operand of the column-sum MMA: [16 x 64] bf16 ones (one K panel, reused)
 // A x2 | Y ring | E x2 | ones | barriers
-constexpr uint32_t kFwdSmem = kTileBytes * (kH + kFwdStages + 2) + kOnesBytes + 256 + 768;
+constexpr uint32_t kFwdSmem = kTileBytes * (kH + kFwdStages + kEBuf) + kOnesBytes + 256 + 768;
 static_assert(kFwdSmem <= 232448, "shared memory budget");
 constexpr int kFwdPoly = PCLIP_FWD_POLY;  // of every 32 exps, this many on the FMA pipes (degree 4)
 constexpr int kFwdEpiWarps = 16;          // 4 warps per SM sub-partition
@@ -669,22 +676,24 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_tiles = smem;                                  // [kH]
   uint8_t* y_tiles = a_tiles + kH * kTileBytes;             // [kFwdStages]
-  uint8_t* e_tiles = y_tiles + kFwdStages * kTileBytes;     // [2], indexed by the row half
-  uint8_t* ones = e_tiles + 2 * kTileBytes;
+  uint8_t* e_tiles = y_tiles + kFwdStages * kTileBytes;     // [kEBuf]
+  uint8_t* ones = e_tiles + kEBuf * kTileBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(ones + kOnesBytes);
   uint64_t* a_full = bars;                   // 1
   uint64_t* y_full = a_full + 1;             // kFwdStages
   uint64_t* y_empty = y_full + kFwdStages;   // kFwdStages
   uint64_t* s_full = y_empty + kFwdStages;   // kSBuf
   uint64_t* s_empty = s_full + kSBuf;        // kSBuf
-  uint64_t* e_full = s_empty + kSBuf;        // 2
-  uint64_t* e_empty = e_full + 2;            // 2
-  uint64_t* c_full = e_empty + 2;            // 2
+  uint64_t* e_full = s_empty + kSBuf;        // kEBuf
+  uint64_t* e_empty = e_full + kEBuf;        // kEBuf
+  uint64_t* c_full = e_empty + kEBuf;        // 2
   uint64_t* c_empty = c_full + 2;            // 2
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c_empty + 2);
   if (threadIdx.x == 0 && reinterpret_cast<uint8_t*>(tmem_slot + 1) > smem_raw + kFwdSmem) __trap();  // alignment slack
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // the warp index through a shuffle: provably warp-uniform, so the role branches and the MMA warp's loop state are
+  // uniform (uniform registers feed tcgen05.mma directly instead of an elect / R2UR loop per operand)
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   long long* tr = (args.trace && blockIdx.x == 0 && blockIdx.y == 0) ? args.trace : nullptr;
   if (threadIdx.x == 0) {
     mbar_init(a_full, 1);
@@ -696,9 +705,11 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
       mbar_init(&s_full[i], 1);
       mbar_init(&s_empty[i], 32 * kFwdEpiWarps);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kEBuf; ++i) {
       mbar_init(&e_full[i], 32 * kFwdEpiWarps);
       mbar_init(&e_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
       mbar_init(&c_full[i], 1);
       mbar_init(&c_empty[i], 128);
     }
@@ -726,7 +737,6 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
         const int stage = t % kFwdStages;
         mbar_wait(&y_empty[stage], ((uint32_t)(t / kFwdStages) & 1u) ^ 1u);
         mbar_arrive_expect_tx(&y_full[stage], kTileBytes);
-        PCLIP_TRACE(0, t * nh);
         const int32_t col0 = (tile_begin + t) * kTile;
         uint8_t* dst = y_tiles + (size_t)stage * kTileBytes;
         tma_load_2d(dst, &tb, &y_full[stage], 0, col0);
@@ -734,54 +744,55 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && ntiles > 0) {
+    if (ntiles > 0) {   // the whole warp runs the issue loop; one elected lane issues each tcgen05 instruction
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, 0, 0);  // S = A . Y^T
       constexpr uint32_t idesc_c = make_idesc_bf16(kTile, 16, 1, 0);     // C[col, :] = sum_rows E[row, col] (E^T . ones)
-      const uint32_t ones_addr = smem_u32(ones);
+      const uint64_t od = kmajor_base(smem_u32(ones));
       const int n_items = ntiles * nh;
       mbar_wait(a_full, 0);
-      int us = 0, uc = 0;                       // next score item / next column-sum item
-      int s_t = 0, s_h = 0, c_t = 0, c_h = 0;   // their (tile, half)
-      while (uc < n_items) {
-        // column sums first: they free the E buffer and are short
-        if (uc < us) {
-          bool ready = mbar_test(&e_full[c_h], (uint32_t)c_t & 1u);
-          if (ready && c_h == 0) ready = mbar_test(&c_empty[c_t & 1], ((uint32_t)(c_t >> 1) & 1u) ^ 1u);
-          if (ready) {
-            tc_fence_after_sync();
-            PCLIP_TRACE(2, uc);
-            const uint32_t e_addr = smem_u32(e_tiles + (size_t)c_h * kTileBytes);
+      // Fixed issue order with blocking waits: S runs kSBuf items ahead; the column sums of item u go out as soon as
+      // its exp tile is complete, followed by the score MMA that reuses the accumulator item u released long before.
+      // (A polling loop here lost ~1000 clk per item: the issuing thread shares its scheduler with four epilogue
+      // warps and was starved while they were busy, profiles/r01c fwd trace.)
+      auto issue_s = [&](int u) {
+        const int t = u / nh, h = u - t * nh;
+        const int sb = u % kSBuf, stage = t % kFwdStages;
+        mbar_wait(&s_empty[sb], ((uint32_t)(u / kSBuf) & 1u) ^ 1u);
+        if (h == 0) mbar_wait(&y_full[stage], (uint32_t)(t / kFwdStages) & 1u);
+        tc_fence_after_sync();
+        if (lane == 0) PCLIP_TRACE(1, u);
+        const uint64_t yd = kmajor_base(smem_u32(y_tiles + (size_t)stage * kTileBytes));
+        const uint64_t ad = kmajor_base(smem_u32(a_tiles + (size_t)h * kTileBytes));
+        if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k)
-              umma_bf16_ss(tmem_c + (uint32_t)(c_t & 1) * 16u, mnmajor_desc(e_addr, k),
-                           make_smem_desc_sw128(ones_addr + (uint32_t)(k & 3) * 32u, 16, 1024), idesc_c,
-                           (c_h > 0 || k > 0) ? 1u : 0u);
-            umma_commit(&e_empty[c_h]);
-            if (c_h == nh - 1) umma_commit(&c_full[c_t & 1]);
-            ++uc;
-            if (++c_h == nh) { c_h = 0; ++c_t; }
-            continue;
-          }
+          for (int k = 0; k < 8; ++k)
+            umma_bf16_ss(tmem_base + (uint32_t)sb * kTile, kmajor_step(ad, k), kmajor_step(yd, k), idesc_s, k > 0 ? 1u : 0u);
+          if (h == nh - 1) umma_commit(&y_empty[stage]);
+          umma_commit(&s_full[sb]);
         }
-        if (us < n_items) {
-          const int sb = us % kSBuf, stage = s_t % kFwdStages;
-          bool ready = mbar_test(&s_empty[sb], ((uint32_t)(us / kSBuf) & 1u) ^ 1u);
-          if (ready && s_h == 0) ready = mbar_test(&y_full[stage], (uint32_t)(s_t / kFwdStages) & 1u);
-          if (ready) {
-            tc_fence_after_sync();
-            PCLIP_TRACE(1, us);
-            const uint32_t y_addr = smem_u32(y_tiles + (size_t)stage * kTileBytes);
-            const uint32_t a_addr = smem_u32(a_tiles + (size_t)s_h * kTileBytes);
+        __syncwarp();
+        if (lane == 0) PCLIP_TRACE(7, u);
+      };
+      for (int u = 0; u < min(kSBuf, n_items); ++u) issue_s(u);
+      for (int u = 0; u < n_items; ++u) {
+        const int t = u / nh, h = u - t * nh;
+        const int eb = u % kEBuf;
+        mbar_wait(&e_full[eb], (uint32_t)(u / kEBuf) & 1u);
+        if (h == 0) mbar_wait(&c_empty[t & 1], ((uint32_t)(t >> 1) & 1u) ^ 1u);
+        tc_fence_after_sync();
+        if (lane == 0) PCLIP_TRACE(2, u);
+        const uint64_t ed = mnmajor_base(smem_u32(e_tiles + (size_t)eb * kTileBytes));
+        if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k)
-              umma_bf16_ss(tmem_base + (uint32_t)sb * kTile, kmajor_desc(a_addr, k), kmajor_desc(y_addr, k), idesc_s,
-                           k > 0 ? 1u : 0u);
-            if (s_h == nh - 1) umma_commit(&y_empty[stage]);
-            umma_commit(&s_full[sb]);
-            ++us;
-            if (++s_h == nh) { s_h = 0; ++s_t; }
-          }
+          for (int k = 0; k < 8; ++k)
+            umma_bf16_ss(tmem_c + (uint32_t)(t & 1) * 16u, mnmajor_step(ed, k), desc_advance(od, (uint32_t)(k & 3) * 32u),
+                         idesc_c, (h > 0 || k > 0) ? 1u : 0u);
+          umma_commit(&e_empty[eb]);
+          if (h == nh - 1) umma_commit(&c_full[t & 1]);
         }
+        __syncwarp();
+        if (lane == 0) PCLIP_TRACE(0, u);
+        if (u + kSBuf < n_items) issue_s(u + kSBuf);
       }
     }
   } else {
@@ -804,8 +815,8 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
       tc_fence_before_sync();
       mbar_arrive(&c_empty[buf]);
     };
-    int sb = 0;
-    uint32_t sph = 0;
+    int sb = 0, eb = 0;
+    uint32_t sph = 0, eph = 0;
     for (int t = 0; t < ntiles; ++t) {
       const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
 #pragma unroll
@@ -867,15 +878,16 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
             }
           }
           if (threadIdx.x == 64) PCLIP_TRACE(5, t * nh + h);
-          mbar_wait(&e_empty[h], ((uint32_t)t & 1u) ^ 1u);   // the column-sum MMA of item (t-1, h) has consumed E[h]
-          const uint32_t panel = e_base + (uint32_t)h * kTileBytes + (uint32_t)(quarter >> 1) * kPanelBytes;
+          mbar_wait(&e_empty[eb], eph ^ 1u);   // the column-sum MMA of item u - kEBuf has consumed this buffer
+          const uint32_t panel = e_base + (uint32_t)eb * kTileBytes + (uint32_t)(quarter >> 1) * kPanelBytes;
 #pragma unroll
           for (int g = 0; g < 4; ++g)
             st_shared_v4(panel + sw128_offset((uint32_t)i, (uint32_t)((quarter & 1) * 4 + g)), packed[4 * g],
                          packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
           fence_proxy_async_smem();
-          mbar_arrive(&e_full[h]);
+          mbar_arrive(&e_full[eb]);
           if (threadIdx.x == 64) PCLIP_TRACE(6, t * nh + h);
+          if (++eb == kEBuf) { eb = 0; eph ^= 1u; }
         }
       }
       if (quarter == 0 && t > 0) flush_cols(t - 1);   // one tile behind: never waits on the MMA just requested
@@ -1095,10 +1107,10 @@ int tc2_sumexp(const void* a, const void* b, int64_t Ma, int64_t Nb, int64_t dia
     cudaFree(trace);
     if (FILE* f = fopen(trace_path, "w")) {
       long long t0 = h[1 * kTraceItems];
-      fprintf(f, "# item tma_issue s_issue c_issue epi_sfull epi_loaded epi_math_done epi_done (clocks since S(0) issue)\n");
+      fprintf(f, "# item c_issued s_issue c_issue epi_sfull epi_loaded epi_math_done epi_done s_issued (clocks since S(0) issue)\n");
       for (int u = 0; u < kTraceItems; ++u) {
         fprintf(f, "%3d", u);
-        for (int ev : {0, 1, 2, 3, 4, 5, 6}) fprintf(f, " %8lld", h[ev * kTraceItems + u] ? h[ev * kTraceItems + u] - t0 : -1);
+        for (int ev : {0, 1, 2, 3, 4, 5, 6, 7}) fprintf(f, " %8lld", h[ev * kTraceItems + u] ? h[ev * kTraceItems + u] - t0 : -1);
         fprintf(f, "\n");
       }
       fclose(f);

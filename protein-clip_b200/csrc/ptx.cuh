@@ -205,6 +205,16 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uin
   return d;
 }
 
+// The descriptor of the same operand layout `byte_off` bytes further on: one 32-bit add on the start-address field
+// (16-byte units; no carry out of the field while addresses stay below 256 KB) instead of a rebuilt descriptor.
+// The issuing thread's dependent instruction chain per tcgen05.mma is what paces N <= 128 MMAs: with descriptors
+// rebuilt from addresses per MMA an M128 N128 K16 MMA cost 85-113 clk, with a base descriptor + constant 64.0
+// (tools/probe_issue.cu).
+__device__ __forceinline__ uint64_t desc_advance(uint64_t desc, uint32_t byte_off) {
+  const uint32_t lo = static_cast<uint32_t>(desc) + (byte_off >> 4);
+  return (desc & 0xffffffff00000000ull) | lo;
+}
+
 // Instruction descriptor for kind::f16, BF16 x BF16 -> FP32 accumulate.
 //   bit 4      c_format = F32
 //   bits 7,10  a/b format = BF16

@@ -10,18 +10,19 @@ using namespace pclip;
 // mode 0: S-like  M128 N128, A K-major, B K-major      mode 1: PV-like M128 N128, A K-major, B MN-major
 // mode 2: C-like  M128 N16,  A MN-major, B K-major     mode 3: M128 N256 both K-major
 // mode 4: M128 N64 both K-major                        mode 5: S-like with an idle second thread polling smem
-__global__ void probe(int mode, int reps, long long* cycles, int side /* 0 none, 1 LDTM, 2 st.shared, 3 both */) {
+__global__ void probe(int mode, int reps, long long* cycles, int side /* 0 none, 1 LDTM, 2 st.shared, 3 both */, int uniform) {
   __shared__ volatile int done;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a = smem;               // 32 KB: [128][64] x 2 panels
   uint8_t* b = smem + 32768;       // 64 KB: up to N = 256
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 32768 * 3);
-  uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 1);
+  uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 2);
   for (int i = threadIdx.x; i < 32768 * 3 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
   if (threadIdx.x == 0) {
     done = 0;
     mbar_init(bar, 1);
+    mbar_init(bar + 1, 1);
     fence_mbar_init();
   }
   fence_proxy_async_smem();
@@ -30,10 +31,13 @@ __global__ void probe(int mode, int reps, long long* cycles, int side /* 0 none,
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tm = *slot;
-  if (threadIdx.x == 0) {
+  if (uniform ? threadIdx.x < 32 : threadIdx.x == 0) {
     const uint32_t aa = smem_u32(a), ba = smem_u32(b);
     const long long t0 = clock64();
+    const int mode_in = mode;
     for (int r = 0; r < reps; ++r) {
+      if (mode_in == 6) mode = (r & 1) ? 2 : 0;   // alternate S-like and C-like groups
+      if (mode_in == 7) mode = 0;                // S-like with a commit after every group
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const uint32_t koff = (uint32_t)(k >> 2) * 16384u + (uint32_t)(k & 3) * 32u;
@@ -52,14 +56,14 @@ __global__ void probe(int mode, int reps, long long* cycles, int side /* 0 none,
           bd = make_smem_desc_sw128(ba + (mode == 3 ? (uint32_t)(k >> 2) * 32768u + (uint32_t)(k & 3) * 32u : koff), 16, 1024);
           idesc = make_idesc_bf16(128, mode == 3 ? 256 : (mode == 4 ? 64 : 128), 0, 0);
         }
-        umma_bf16_ss(tm + (uint32_t)(r & 1) * 256u, ad, bd, idesc, k > 0 ? 1u : 0u);
+        if (!uniform || elect_one()) umma_bf16_ss(tm + (uint32_t)(r & 1) * 256u, ad, bd, idesc, k > 0 ? 1u : 0u);
       }
+      if (mode_in == 7 && (!uniform || elect_one())) umma_commit(bar + 1);
     }
-    umma_commit(bar);
+    if (!uniform || elect_one()) umma_commit(bar);
     mbar_wait(bar, 0);
     const long long t1 = clock64();
-    cycles[0] = t1 - t0;
-    done = 1;
+    if (threadIdx.x == 0) { cycles[0] = t1 - t0; done = 1; }
   } else if (threadIdx.x >= 64 && side) {
     // side traffic from the other warps while the MMAs run
     const int warp = threadIdx.x >> 5;
@@ -91,15 +95,16 @@ int main() {
   const int smem = 32768 * 4 + 2048;
   cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   const int reps = 2000;
-  const char* names[] = {"S-like M128 N128 KK", "PV-like M128 N128 K,MN", "C-like M128 N16 MN,K", "M128 N256 KK", "M128 N64 KK"};
-  for (int side = 0; side < 4; ++side)
-  for (int mode = 0; mode < 5; ++mode) {
-    if (side && mode > 1) continue;
-    probe<<<1, side ? 576 : 128, smem>>>(mode, reps, c, side);
+  const char* names[] = {"S-like M128 N128 KK", "PV-like M128 N128 K,MN", "C-like M128 N16 MN,K", "M128 N256 KK", "M128 N64 KK", "?", "alternate S / C groups", "S-like + commit per group"};
+  for (int uniform = 0; uniform < 2; ++uniform)
+  for (int side = 0; side < 4; side += 3)
+  for (int mode = 0; mode < 8; ++mode) {
+    if (mode == 5 || (side && mode > 1 && mode < 6)) continue;
+    probe<<<1, side ? 576 : 128, smem>>>(mode, reps, c, side, uniform);
     cudaError_t e = cudaDeviceSynchronize();
     long long h = 0;
     cudaMemcpy(&h, c, 8, cudaMemcpyDeviceToHost);
-    printf("side %d %-24s: %s  %.1f clk per MMA (K = 16), %.1f clk per 8-MMA tile\n", side, names[mode], cudaGetErrorString(e),
+    printf("uniform %d side %d %-24s: %s  %.1f clk per MMA (K = 16), %.1f clk per 8-MMA tile\n", uniform, side, names[mode], cudaGetErrorString(e),
            (double)h / (reps * 8), (double)h / reps);
   }
   return 0;
