@@ -184,7 +184,7 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
   uint64_t* pv_done = d_full + 1;             // [kH]: the P . Y MMA of the previous tile has finished reading P_h
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + kH);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
   long long* tr = (args.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? args.trace : nullptr;
   if (threadIdx.x == 0) {
     mbar_init(a_full, 1);
@@ -227,19 +227,22 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && ntiles > 0) {
+    if (ntiles > 0) {   // the whole warp runs the issue loop; one elected lane issues each tcgen05 instruction
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, 0, 0);   // S = A . Y^T   (both K-major)
       constexpr uint32_t idesc_g = make_idesc_bf16(kTile, kTile, 0, 1);   // dA += P . Y   (Y tile as MN-major B)
       mbar_wait(a_full, 0);
       auto issue_s = [&](int h, int t) {
         const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kBwdStages) * kTileBytes);
         const uint32_t a_addr = smem_u32(a_tiles + h * kTileBytes);
-        PCLIP_TRACE(0, 2 * t + h);
+        if (lane == 0) PCLIP_TRACE(0, 2 * t + h);
         const uint64_t ad = kmajor_base(a_addr), yd = kmajor_base(y_addr);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          umma_bf16_ss(tmem_base + (uint32_t)h * kTile, kmajor_step(ad, k), kmajor_step(yd, k), idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(&s_full[h]);
+          for (int k = 0; k < 8; ++k)
+            umma_bf16_ss(tmem_base + (uint32_t)h * kTile, kmajor_step(ad, k), kmajor_step(yd, k), idesc_s, k > 0 ? 1u : 0u);
+          umma_commit(&s_full[h]);
+        }
+        __syncwarp();
       };
       mbar_wait(&y_full[0], 0);
       tc_fence_after_sync();
@@ -260,17 +263,20 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
             issue_s(h, t + 1);
           }
           const uint32_t p_addr = smem_u32(p_tiles + h * kTileBytes);
-          PCLIP_TRACE(1, 2 * t + h);
+          if (lane == 0) PCLIP_TRACE(1, 2 * t + h);
           const uint64_t pd = kmajor_base(p_addr), yd = mnmajor_base(y_addr);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
-            umma_bf16_ss(tmem_base + (uint32_t)(kH + h) * kTile, kmajor_step(pd, k), mnmajor_step(yd, k), idesc_g,
-                         (t > 0 || k > 0) ? 1u : 0u);
-          umma_commit(&pv_done[h]);
+            for (int k = 0; k < 8; ++k)
+              umma_bf16_ss(tmem_base + (uint32_t)(kH + h) * kTile, kmajor_step(pd, k), mnmajor_step(yd, k), idesc_g,
+                           (t > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&pv_done[h]);
+            if (h == nh - 1) umma_commit(&y_empty[t % kBwdStages]);
+            if (h == nh - 1 && t == ntiles - 1) umma_commit(d_full);
+          }
+          __syncwarp();
         }
-        umma_commit(&y_empty[t % kBwdStages]);
       }
-      umma_commit(d_full);
     }
   } else {
     // 16 epilogue warps: row half h x lane quadrant q x column half ch (4 warps per SM sub-partition)
@@ -297,6 +303,11 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         for (int c = 0; c < 2; ++c) {
           uint32_t v[32];
           tmem_ld_32x32b_x32(taddr + c * 32, v);
+          const uint32_t cs_addr = smem_u32(cs + ch * 64 + c * 32);   // explicit shared-space loads (see tc3_grad_kernel)
+          uint64_t cs2[16];
+#pragma unroll
+          for (int e = 0; e < 32; e += 4)
+            asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(cs2[e >> 1]), "=l"(cs2[(e >> 1) + 1]) : "r"(cs_addr + 4u * e) : "memory");
           tmem_ld_wait();
           uint32_t packed[16];
 #pragma unroll
@@ -310,7 +321,7 @@ tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
               e0 = ex2_approx(y0);
               e1 = ex2_approx(y1);
             }
-            const uint64_t w = add2(rinv2, *reinterpret_cast<const uint64_t*>(&cs[ch * 64 + c * 32 + e]));
+            const uint64_t w = add2(rinv2, cs2[e >> 1]);
             float p0, p1;
             unpack2(mul2(pack2(e0, e1), w), p0, p1);
             packed[e >> 1] = bf16x2_bits(p0, p1);
@@ -439,7 +450,7 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_full + 1);
   if (threadIdx.x == 0 && reinterpret_cast<uint8_t*>(tmem_slot + 1) > smem_raw + kSmem3) __trap();  // alignment slack
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
   long long* tr = (args.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? args.trace : nullptr;
   if (threadIdx.x == 0) {
     mbar_init(a_full, 1);
@@ -484,7 +495,7 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && ntiles > 0) {
+    if (ntiles > 0) {   // the whole warp runs the issue loop; one elected lane issues each tcgen05 instruction
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kRows, 0, 0);   // S^T = Y . A^T      (both K-major)
       constexpr uint32_t idesc_g = make_idesc_bf16(kTile, kRows, 1, 1);   // dA^T += Y^T . P^T  (both MN-major)
       const uint64_t ad = kmajor_base(smem_u32(a_rows)), pd = mnmajor_base(smem_u32(p_t));
@@ -494,28 +505,34 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
         mbar_wait(&y_full[stage], (uint32_t)(t / kStages) & 1u);
         if (t > 0) mbar_wait(s_free, (uint32_t)(t - 1) & 1u);
         tc_fence_after_sync();
-        PCLIP_TRACE(0, t);
+        if (lane == 0) PCLIP_TRACE(0, t);
         const uint64_t yd = kmajor_base(smem_u32(y_tiles + (size_t)stage * kTileBytes));
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          umma_bf16_ss(tmem_s, kmajor_step(yd, k), desc_advance(ad, (uint32_t)(k >> 2) * (kABytes / 2) + (uint32_t)(k & 3) * 32u),
-                       idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(s_full);
+          for (int k = 0; k < 8; ++k)
+            umma_bf16_ss(tmem_s, kmajor_step(yd, k), desc_advance(ad, (uint32_t)(k >> 2) * (kABytes / 2) + (uint32_t)(k & 3) * 32u),
+                         idesc_s, k > 0 ? 1u : 0u);
+          umma_commit(s_full);
+        }
+        __syncwarp();
       };
       issue_s(0);
       for (int t = 0; t < ntiles; ++t) {
         if (t + 1 < ntiles) issue_s(t + 1);
         mbar_wait(p_full, (uint32_t)t & 1u);
         tc_fence_after_sync();
-        PCLIP_TRACE(1, t);
+        if (lane == 0) PCLIP_TRACE(1, t);
         const uint64_t yd = mnmajor_base(smem_u32(y_tiles + (size_t)(t % kStages) * kTileBytes));
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          umma_bf16_ss(tmem_d, mnmajor_step(yd, k), mnmajor_step(pd, k), idesc_g, (t > 0 || k > 0) ? 1u : 0u);
-        umma_commit(pv_done);
-        umma_commit(&y_empty[t % kStages]);
+          for (int k = 0; k < 8; ++k)
+            umma_bf16_ss(tmem_d, mnmajor_step(yd, k), mnmajor_step(pd, k), idesc_g, (t > 0 || k > 0) ? 1u : 0u);
+          umma_commit(pv_done);
+          umma_commit(&y_empty[t % kStages]);
+          if (t == ntiles - 1) umma_commit(d_full);
+        }
+        __syncwarp();
       }
-      umma_commit(d_full);
     }
   } else {
     // 16 epilogue warps: lane quadrant q (columns j of the tile) x row group g (64 rows i each)
@@ -549,9 +566,9 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
 #pragma unroll
         for (int e = 0; e < 32; e += PCLIP_RINV_LD / 32) {
           if (PCLIP_RINV_LD == 128)
-            asm("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(rs2[e >> 1]), "=l"(rs2[(e >> 1) + 1]) : "r"(rs_addr + 4u * e));
+            asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(rs2[e >> 1]), "=l"(rs2[(e >> 1) + 1]) : "r"(rs_addr + 4u * e) : "memory");
           else
-            asm("ld.shared.b64 %0, [%1];" : "=l"(rs2[e >> 1]) : "r"(rs_addr + 4u * e));
+            asm volatile("ld.shared.b64 %0, [%1];" : "=l"(rs2[e >> 1]) : "r"(rs_addr + 4u * e) : "memory");
         }
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
