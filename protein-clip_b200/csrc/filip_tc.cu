@@ -30,14 +30,19 @@ constexpr int kH = 2;                       // row tiles per CTA
 constexpr int kRows = kH * kTile;
 constexpr int kThreads = 64 + 32 * 4 * kH;  // TMA warp, MMA warp, 4 warps per row tile
 
-__device__ __forceinline__ uint64_t tile_desc(uint32_t tile_smem_addr, int k) {
-  const uint32_t addr = tile_smem_addr + (uint32_t)(k >> 2) * kPanelBytes + (uint32_t)(k & 3) * 32u;
-  return make_smem_desc_sw128(addr, 16, 1024);
-}
+// One 128 x 128 x 128 tile product.  Called by the whole (converged) MMA warp: the descriptors are built once per tile
+// and advanced by constants per k-step, and one elected lane issues, so the operands stay in uniform registers (a
+// descriptor rebuilt per MMA behind `if (lane == 0)` paced these MMAs at 85-113 clk instead of 64, tools/probe_issue.cu).
 __device__ __forceinline__ void issue_tile(uint32_t d, uint32_t a_addr, uint32_t b_addr, uint32_t idesc, bool acc) {
+  const uint64_t ad = make_smem_desc_sw128(a_addr, 16, 1024), bd = make_smem_desc_sw128(b_addr, 16, 1024);
+  if (elect_one()) {
 #pragma unroll
-  for (int k = 0; k < kDim / 16; ++k)
-    umma_bf16_ss(d, tile_desc(a_addr, k), tile_desc(b_addr, k), idesc, (k > 0 || acc) ? 1u : 0u);
+    for (int k = 0; k < kDim / 16; ++k) {
+      const uint32_t off = (uint32_t)(k >> 2) * kPanelBytes + (uint32_t)(k & 3) * 32u;
+      umma_bf16_ss(d, desc_advance(ad, off), desc_advance(bd, off), idesc, (k > 0 || acc) ? 1u : 0u);
+    }
+  }
+  __syncwarp();
 }
 }  // namespace fl
 
@@ -117,7 +122,7 @@ tc_filip_max_kernel(const __grid_constant__ CUtensorMap tx, const __grid_constan
   uint64_t* t_empty = t_full + 2 * kH;       // [kH][2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2 * kH);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
   if (threadIdx.x == 0) {
     mbar_init(a_full, 1);
     for (int i = 0; i < kFwdStages; ++i) {
@@ -160,7 +165,7 @@ tc_filip_max_kernel(const __grid_constant__ CUtensorMap tx, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && nh > 0) {
+    if (nh > 0) {   // whole warp; tcgen05 instructions go out from one elected lane
       constexpr uint32_t idesc = make_idesc_bf16(kTile, kTile, 0, 0);
       mbar_wait(a_full, 0);
       int it = 0;
@@ -178,9 +183,12 @@ tc_filip_max_kernel(const __grid_constant__ CUtensorMap tx, const __grid_constan
             tc_fence_after_sync();
             issue_tile(tmem_base + (uint32_t)(h * 2 + buf) * kTile, smem_u32(a_tiles + h * kTileBytes), b_addr, idesc,
                        false);
-            umma_commit(&t_full[h * 2 + buf]);
+            if (elect_one()) {
+              umma_commit(&t_full[h * 2 + buf]);
+              if (h == nh - 1) umma_commit(&b_empty[stage]);
+            }
+            __syncwarp();
           }
-          umma_commit(&b_empty[stage]);
         }
       }
     }
@@ -293,7 +301,7 @@ tc_filip_grad_kernel(const __grid_constant__ CUtensorMap tyT, const FilipBwdArgs
   uint64_t* d_full = p_empty + 2 * kH;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_full + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBwdStages; ++i) {
       mbar_init(&y_full[i], 1);
@@ -330,7 +338,7 @@ tc_filip_grad_kernel(const __grid_constant__ CUtensorMap tyT, const FilipBwdArgs
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && nh > 0) {
+    if (nh > 0) {   // whole warp; tcgen05 instructions go out from one elected lane
       constexpr uint32_t idesc = make_idesc_bf16(kTile, kTile, 0, 0);
       int it = 0;
       for (int by = 0; by < args.By; ++by) {
@@ -347,12 +355,16 @@ tc_filip_grad_kernel(const __grid_constant__ CUtensorMap tyT, const FilipBwdArgs
             tc_fence_after_sync();
             issue_tile(tmem_base + (uint32_t)h * kTile, smem_u32(p_tiles + (size_t)(h * 2 + buf) * kTileBytes), y_addr,
                        idesc, it > 0);
-            umma_commit(&p_empty[h * 2 + buf]);
+            if (elect_one()) {
+              umma_commit(&p_empty[h * 2 + buf]);
+              if (h == nh - 1) umma_commit(&y_empty[stage]);
+            }
+            __syncwarp();
           }
-          umma_commit(&y_empty[stage]);
         }
       }
-      umma_commit(d_full);
+      if (elect_one()) umma_commit(d_full);
+      __syncwarp();
     }
   } else {
     // ---- builder + final epilogue: 128 threads per row tile ----

@@ -36,9 +36,10 @@ constexpr int kEpiThreadsPerTile = 128;
 constexpr uint32_t kSmemBytes = kTileBytes * (kQTiles + kStages) + kMaxCand * kRows * 8 + 256 + 1024;
 static_assert(kSmemBytes <= 232448, "shared memory budget");
 
-__device__ __forceinline__ uint64_t tile_desc(uint32_t tile_smem_addr, int k) {
-  const uint32_t addr = tile_smem_addr + (uint32_t)(k >> 2) * kPanelBytes + (uint32_t)(k & 3) * 32u;
-  return make_smem_desc_sw128(addr, 16, 1024);
+// K-major tile descriptor, built once per tile and advanced per k-step by a constant (ptx.cuh desc_advance)
+__device__ __forceinline__ uint64_t tile_desc_base(uint32_t tile_smem_addr) { return make_smem_desc_sw128(tile_smem_addr, 16, 1024); }
+__device__ __forceinline__ uint64_t tile_desc_step(uint64_t base, int k) {
+  return desc_advance(base, (uint32_t)(k >> 2) * kPanelBytes + (uint32_t)(k & 3) * 32u);
 }
 __device__ __forceinline__ float max3(float a, float b, float c) {
   float r;
@@ -109,7 +110,7 @@ tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
   uint64_t* t_empty = t_full + 2 * kQTiles;      // [kQTiles][2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2 * kQTiles);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: the MMA warp's loop state lives in uniform registers
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
@@ -151,7 +152,7 @@ tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {   // the whole warp runs the issue loop; one elected lane issues each tcgen05 instruction
       constexpr uint32_t idesc = make_idesc_bf16(kTile, kTile, 0, 0);
       mbar_wait(a_full, 0);
       for (int t = 0; t < ntiles; ++t) {
@@ -160,19 +161,22 @@ tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
         const int buf = t & 1;
         const uint32_t bphase = (uint32_t)(t >> 1) & 1u;
         mbar_wait(&b_full[stage], phase);
-        const uint32_t b_addr = smem_u32(b_tiles + (size_t)stage * kTileBytes);
+        const uint64_t bd = tile_desc_base(smem_u32(b_tiles + (size_t)stage * kTileBytes));
 #pragma unroll
         for (int h = 0; h < kQTiles; ++h) {
           mbar_wait(&t_empty[h * 2 + buf], bphase ^ 1u);
           tc_fence_after_sync();
-          const uint32_t a_addr = smem_u32(a_tiles + h * kTileBytes);
+          const uint64_t ad = tile_desc_base(smem_u32(a_tiles + h * kTileBytes));
           const uint32_t d = tmem_base + (uint32_t)(h * 2 + buf) * kTile;
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kDim / 16; ++k)
-            umma_bf16_ss(d, tile_desc(a_addr, k), tile_desc(b_addr, k), idesc, k > 0 ? 1u : 0u);
-          umma_commit(&t_full[h * 2 + buf]);
+            for (int k = 0; k < kDim / 16; ++k)
+              umma_bf16_ss(d, tile_desc_step(ad, k), tile_desc_step(bd, k), idesc, k > 0 ? 1u : 0u);
+            umma_commit(&t_full[h * 2 + buf]);
+            if (h == kQTiles - 1) umma_commit(&b_empty[stage]);
+          }
+          __syncwarp();
         }
-        umma_commit(&b_empty[stage]);
       }
     }
   } else {
