@@ -398,7 +398,8 @@ def main():
                 "d2h_bytes_per_step": w.d2h * dist.world, "ms_per_step": round(ms_e2e / args.steps, 4)},
         "gpu_launches": launches,
         "step_tflops_algorithmic": round(6.0 * w.B * w.B * w.D / (ms / args.steps * 1e-3) / 1e12, 1),
-        "step_frac_of_tensor_peak": round(6.0 * w.B * w.B * w.D / (ms / args.steps * 1e-3) / 1e12 / peaks["tc"], 4),
+        "step_frac_of_tensor_peak": round(6.0 * w.B * w.B * w.D / (ms / args.steps * 1e-3) / 1e12 / peaks["tc"]
+                                          / max(args.gpus, 1), 4),   # whole-job flops over N GPUs' peak
     }
     if dist.rank == 0 and dist.world == 1 and not args.no_extras:
         del w.plan, w.job

@@ -948,24 +948,19 @@ __global__ void col_reduce_kernel(const float* __restrict__ colpart, int nrb, in
   colsum[j] = s;
 }
 
-static void plan2(int64_t row_blocks, int64_t ntiles, int n_sides, int max_split, int* nsplit, int* tps) {
-  int64_t want = ceil_div(2 * 148, row_blocks * n_sides);
-  want = std::min<int64_t>(std::min<int64_t>(want, ntiles), max_split);
-  if (want < 1 || ntiles <= 2) want = 1;
-  *tps = (int)ceil_div(ntiles, want);
-  *nsplit = (int)ceil_div(ntiles, *tps);
-}
-
 // Column splits so that the CTA count fills whole waves of the SMs (one CTA per SM): 512 row blocks on 148 SMs are
-// 3.46 waves (87 % of the last wave's SM-time used); split in two they are 6.92 (99 %).
+// 3.46 waves (87 % of the last wave's SM-time used); split in two they are 6.92 (99 %).  A row shard of a multi-GPU run
+// has fewer row blocks than SMs (64 at B = 65 536 on 8 GPUs): there the split count is searched further (9 splits
+// -> 576 CTAs = 3.9 waves) instead of "about two CTAs per SM" (5 splits -> 2.2 waves, a third of the last wave idle).
 static void plan_waves(int64_t row_blocks, int64_t ntiles, int n_sides, int max_split, int* nsplit, int* tps) {
   const int sms = std::max(device_sm_count(), 1);
-  if (row_blocks * n_sides < sms) return plan2(row_blocks, ntiles, n_sides, 8 * max_split, nsplit, tps);
+  const int64_t base = row_blocks * n_sides;
+  const int cap = base < sms ? 8 * max_split : max_split;
   double best = 0.0;
   int best_ns = 1;
-  for (int ns = 1; ns <= max_split && ns * 4 <= ntiles; ++ns) {
+  for (int ns = 1; ns <= cap && (ns == 1 || ns * 4 <= ntiles); ++ns) {
     const int64_t t = ceil_div(ntiles, (int64_t)ns);                       // tiles per split
-    const int64_t ctas = row_blocks * n_sides * ceil_div(ntiles, t);
+    const int64_t ctas = base * ceil_div(ntiles, t);
     const double eff = (double)ctas / (double)(ceil_div(ctas, (int64_t)sms) * sms);
     if (eff > best + 0.02) {
       best = eff;

@@ -199,6 +199,18 @@ class ClipPlan:
         # 1/R and 1/C of ALL rows (the gradient kernel needs the other side's normalisers for every column)
         self.rinv_f = self.rinv if self.local_is_full else torch.empty(Nb, **f32)
         self.cinv_f = self.cinv if self.local_is_full else torch.empty(Nb, **f32)
+        if self.single_pass and not self.local_is_full:
+            # Row shard: what this rank owes the others after the forward sweep is ONE contiguous record
+            # [C partial (Nb) | R (Ma) | S_ii (Ma)] (pclip/sharded.py gathers it in one collective); the forward kernel
+            # writes straight into it, and 1/R, 1/C of the local rows are views of the full-length results.
+            self.stats_l = torch.zeros(Nb + 2 * Ma, **f32)
+            self.colsum_f = self.stats_l[:Nb]
+            self.rowsum = self.stats_l[Nb:Nb + Ma]
+            self.diag = self.stats_l[Nb + Ma:]
+            self.rowsum_full, self.colsum_full, self.diag_full = (torch.empty(Nb, **f32) for _ in range(3))
+            self.row_lse_f, self.col_lse_f = torch.empty(Nb, **f32), torch.empty(Nb, **f32)
+            self.rinv = self.rinv_f[diag_offset:diag_offset + Ma]
+            self.cinv = self.cinv_f[diag_offset:diag_offset + Ma]
         self.loss = torch.zeros(1, **f32)
         self.dx, self.dy = torch.empty(Ma, D, **f32), torch.empty(Ma, D, **f32)
         lib = L.lib()
@@ -250,6 +262,19 @@ class ClipPlan:
         L.check(L.lib().pclip_clip_finalize(L.ptr(self.rowsum), L.ptr(self.colsum), L.ptr(self.diag), self.Ma,
                                             0.5 / B_total, L.ptr(self.row_lse), L.ptr(self.col_lse), L.ptr(self.rinv),
                                             L.ptr(self.cinv), L.ptr(self.loss), self._st()))
+
+    def finalize_full(self, stats_all: torch.Tensor, B_total: int):
+        """Row shard, after the all-gather of every rank's [C partial | R | S_ii] record (`stats_all` [P, Nb + 2 Ma]):
+        reduce the column partials, lay R and S_ii out by global row, and finalise ALL rows here -- the loss comes out
+        global on every rank and 1/R, 1/C of every row are local, so no further exchange is needed."""
+        Nb, Ma = self.Nb, self.Ma
+        P = stats_all.shape[0]
+        torch.sum(stats_all[:, :Nb], dim=0, out=self.colsum_full)
+        self.rowsum_full.view(P, Ma).copy_(stats_all[:, Nb:Nb + Ma])
+        self.diag_full.view(P, Ma).copy_(stats_all[:, Nb + Ma:])
+        L.check(L.lib().pclip_clip_finalize(L.ptr(self.rowsum_full), L.ptr(self.colsum_full), L.ptr(self.diag_full), Nb,
+                                            0.5 / B_total, L.ptr(self.row_lse_f), L.ptr(self.col_lse_f),
+                                            L.ptr(self.rinv_f), L.ptr(self.cinv_f), L.ptr(self.loss), self._st()))
 
     def grad(self, B_total: int, gscale: torch.Tensor | None = None):
         sides = (L.BwdSide * 2)(

@@ -13,6 +13,8 @@ class OracleStages:
         self.loss, self.dx, self.dy = z(1), z(Ma, D), z(Ma, D)
         if Ma == Nb:
             self.xf, self.yf, self.rinv_f, self.cinv_f = self.xl, self.yl, self.rinv, self.cinv
+        elif single_pass:
+            self.stats_l = z(Nb + 2 * Ma)        # [C partial | R | S_ii], as pclip.ops.ClipPlan lays it out
 
     def pack(self, xs, ys):
         self.xl.copy_(torch.cat(list(xs)).double())
@@ -31,6 +33,20 @@ class OracleStages:
         self.R = e.sum(1)
         self.colsum_f = e.sum(0)                             # partial over this rank's rows
         self.diag = (self.xl * self.yf[self.off:self.off + self.Ma]).sum(-1)
+        if hasattr(self, "stats_l"):
+            self.stats_l.copy_(torch.cat([self.colsum_f, self.R, self.diag]))
+
+    def finalize_full(self, stats_all, B):
+        Nb, Ma = self.Nb, self.Ma
+        C = stats_all[:, :Nb].sum(0)
+        R = stats_all[:, Nb:Nb + Ma].reshape(-1)
+        d = stats_all[:, Nb + Ma:].reshape(-1)
+        self.loss[0] = (R.log() + C.log() - 2 * d).sum() / (2 * B)      # global on every rank
+        self.rinv_f.copy_(1 / R)
+        self.cinv_f.copy_(1 / C)
+        pos = slice(self.off, self.off + Ma)
+        self.rinv.copy_(self.rinv_f[pos])
+        self.cinv.copy_(self.cinv_f[pos])
 
     def take_local_colsum(self):
         self.C = self.colsum_f[self.off:self.off + self.Ma].clone()
