@@ -84,3 +84,97 @@ class ShardedClip:
                 dist.all_gather_into_tensor(s.cinv_f, s.cinv, group=g)
         rec("grad", 0); s.grad(self.B, gscale); rec("grad", 1)
         return s.loss, s.dx, s.dy
+
+
+class ShardedFilip:
+    """FILIP token-wise loss with the A-batch rows sharded over the ranks (configs[2]).
+
+    Both FILIP losses are row-wise (ref: modules/training_utils_filip.py:26-39 -- simB is NOT transposed), so row a of
+    the loss needs hA[a] and ALL of hB: rank p keeps its B/P samples of A, all-gathers hB (+ masks), and evaluates the
+    [B/P, B] blocks of simA / simB, both log-sum-exps and dhA completely locally.  What every rank holds only a part of
+    is dhB (each rank's rows contribute to every B sample): one reduce-scatter (sum) returns each rank its own B/P
+    samples of it; the loss and d tau are all-reduced scalars.  Token length TB must be padded to the same value on all
+    ranks.  `backend` (default pclip.ops) supplies `filip_similarity` and `filip_loss`; tests inject the oracle."""
+
+    def __init__(self, group=None, backend=None):
+        self.group = group
+        self.P = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if backend is None:
+            from . import ops as backend
+        self.be = backend
+        self.rs_native = dist.get_backend(group) == "nccl"       # gloo has no reduce-scatter: all-reduce + slice
+
+    def step(self, hA_l, hB_l, maskA_l, maskB_l, tau):
+        """Local samples hA_l [Bl, TA, D], hB_l [Bl, TB, D], right-padded masks [Bl, T*]; tau 0-d.
+        Returns (global loss, dhA_l, dhB_l, dtau) -- the gradients of the GLOBAL mean loss."""
+        g, P, r = self.group, self.P, self.rank
+        Bl = hA_l.shape[0]
+        B = Bl * P
+        hB_src, mB_src = hB_l.detach().contiguous(), maskB_l.contiguous()
+        if P > 1:
+            hB_f = torch.empty((B,) + tuple(hB_src.shape[1:]), dtype=hB_src.dtype, device=hB_src.device)
+            mB_f = torch.empty((B,) + tuple(mB_src.shape[1:]), dtype=mB_src.dtype, device=mB_src.device)
+            dist.all_gather_into_tensor(hB_f, hB_src, group=g)
+            dist.all_gather_into_tensor(mB_f, mB_src, group=g)
+        else:
+            hB_f, mB_f = hB_src.clone(), mB_src
+        hA = hA_l.detach().clone().requires_grad_(True)
+        hB_f.requires_grad_(True)
+        tau_l = torch.as_tensor(tau).detach().clone().to(hA.device).requires_grad_(True)
+        simA, simB = self.be.filip_similarity(hA, hB_f, maskA_l, mB_f, tau_l)
+        # filip_loss is the mean over the LOCAL rows; Bl / B of it is this rank's share of the global mean
+        loss = self.be.filip_loss(simA, simB, diag_offset=r * Bl) * (Bl / B)
+        loss.backward()
+        loss_g, dtau = loss.detach().clone().reshape(1), tau_l.grad.detach().clone().reshape(1)
+        dhB_f = hB_f.grad
+        if P > 1:
+            dist.all_reduce(loss_g, group=g)
+            dist.all_reduce(dtau, group=g)
+            if self.rs_native:
+                dhB_l = torch.empty_like(hB_src)
+                dist.reduce_scatter_tensor(dhB_l, dhB_f.contiguous(), group=g)
+            else:
+                dist.all_reduce(dhB_f, group=g)
+                dhB_l = dhB_f[r * Bl:(r + 1) * Bl].clone()
+        else:
+            dhB_l = dhB_f
+        return loss_g, hA.grad, dhB_l, dtau
+
+
+class ShardedTopk:
+    """Cosine / dot-product top-k over the GPUs of one box (configs[4]).
+
+    mode "queries" (default): the bank is replicated (1.07 GB in bf16 at N = 2^22 fits every GPU), each rank answers
+        its own slice of the queries -- independent units, NO collective; the caller keeps the per-rank results.
+    mode "bank": for banks that do not fit one GPU.  Every rank holds all queries and N / P bank rows, finds its local
+        top-k with GLOBAL indices (`index_base`), and one all-gather of the [Q, k] (index, score) lists is followed by
+        the k-way merge (`pclip_topk_merge`: score descending, ties to the lower global index) on every rank."""
+
+    def __init__(self, k: int, mode: str = "queries", group=None, backend=None):
+        if mode not in ("queries", "bank"):
+            raise ValueError("mode must be 'queries' or 'bank'")
+        self.k, self.mode, self.group = k, mode, group
+        self.P = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if backend is None:
+            from . import ops as backend
+        self.be = backend
+
+    def run(self, q: torch.Tensor, bank: torch.Tensor, rows_before: int | None = None):
+        """mode "queries": q = this rank's queries, bank = the full bank -> (idx, score) of those queries.
+        mode "bank": q = ALL queries, bank = this rank's rows, `rows_before` = number of bank rows on lower ranks
+        (default rank * len(bank): equal shards) -> the global (idx, score) of all queries, identical on every rank."""
+        if self.mode == "queries":
+            idx, score = self.be.topk(q, bank, self.k)[:2]
+            return idx, score
+        base = self.rank * bank.shape[0] if rows_before is None else rows_before
+        idx, score = self.be.topk(q, bank, self.k, index_base=base)[:2]
+        if self.P == 1:
+            return idx, score
+        idx_all = torch.empty((self.P,) + tuple(idx.shape), dtype=idx.dtype, device=idx.device)
+        score_all = torch.empty((self.P,) + tuple(score.shape), dtype=score.dtype, device=score.device)
+        # (concatenation along dim 0 of the flattened view: the layout every backend accepts)
+        dist.all_gather_into_tensor(idx_all.view(-1, idx.shape[-1]), idx.contiguous(), group=self.group)
+        dist.all_gather_into_tensor(score_all.view(-1, score.shape[-1]), score.contiguous(), group=self.group)
+        return self.be.topk_merge(idx_all, score_all)

@@ -53,3 +53,32 @@ def test_emulated_ranks_match_single_gpu(P, B, mode):
     for got, one, want in ((dx, dx1, dxo), (dy, dy1, dyo)):
         assert float((got.double().cpu() - want).abs().max() / want.abs().max()) <= (3e-5 if mode == "f32" else 4e-3)
         assert float((got - one).abs().max() / one.abs().max()) <= 1e-5
+
+
+@pytest.mark.parametrize("P,B", [(2, 2048), (8, 4096)])
+def test_emulated_fused_exchange_matches_single_gpu(P, B):
+    """The one-collective exchange of pclip/sharded.py (record [C partial | R | S_ii] per rank, finalize_full on every
+    rank) with the all-gather done by hand."""
+    from pclip import ops, synth
+    x, y = synth.clip_scaled_embeddings(B, 128, cfg_id=60 + P, trained_like=True)
+    xd, yd = x.cuda(), y.cuda()
+    Ma = B // P
+    plans = [ops.ClipPlan(Ma, B, 128, ops.BF16, "cuda", diag_offset=r * Ma) for r in range(P)]
+    assert all(p.single_pass and hasattr(p, "stats_l") for p in plans)
+    for r, p in enumerate(plans):
+        p.pack([xd[r * Ma:(r + 1) * Ma]], [yd[r * Ma:(r + 1) * Ma]])
+    xf, yf = torch.cat([p.xl for p in plans]), torch.cat([p.yl for p in plans])
+    for p in plans:
+        p.xf.copy_(xf)
+        p.yf.copy_(yf)
+        p.sumexp()
+    stats_all = torch.stack([p.stats_l for p in plans])                               # the single all-gather
+    for p in plans:
+        p.finalize_full(stats_all, B)
+        p.grad(B)
+    l1, dx1, dy1, _, _ = ops.clip_loss_raw([xd], [yd], ops.BF16, True)
+    for p in plans:                                                                   # the loss is global on every rank
+        assert abs(float(p.loss) - float(l1)) <= 1e-6 * abs(float(l1))
+    dx, dy = torch.cat([p.dx for p in plans]), torch.cat([p.dy for p in plans])
+    for got, one in ((dx, dx1), (dy, dy1)):
+        assert float((got - one).abs().max() / one.abs().max()) <= 1e-5
