@@ -334,10 +334,16 @@ class Topk4M:
     bf16 tensor-core candidate selection + exact fp32 re-scoring; queries stream through in batches of Q."""
     name = "topk_4m"
 
-    def __init__(self, dist: Dist, N=1 << 22, Q=1 << 18, k=10):
+    def __init__(self, dist: Dist, N=1 << 22, Q=1 << 18, k=10, q_total=None):
         from pclip import ops, synth
         self.ops, self.N, self.Q, self.k = ops, N, Q, k
-        self.bank, self.q, self.pos = synth.retrieval_bank(N, Q, cfg_id=5, device=dist.dev)
+        self.world = dist.world if q_total else 1
+        if q_total:      # query-sharded: the same seeded bank and query set on every rank, this rank's slice of the queries
+            self.bank, q, pos = synth.retrieval_bank(N, q_total, cfg_id=5, device=dist.dev)
+            self.q, self.pos = q[dist.rank * Q:(dist.rank + 1) * Q].contiguous(), pos[dist.rank * Q:(dist.rank + 1) * Q]
+            del q
+        else:
+            self.bank, self.q, self.pos = synth.retrieval_bank(N, Q, cfg_id=5, device=dist.dev)
         self.plan = ops.TopkPlan(Q, N, 128, k, ops.BF16, dist.dev)
 
     def step(self):
@@ -346,11 +352,13 @@ class Topk4M:
     def report(self, dist, peaks, steps=3, warmup=1):
         self.ops.reset_launch_count()
         ms = timed(dist, self.step, steps, warmup) / steps
-        flops = 2.0 * self.Q * self.N * 128
+        Qall = self.Q * self.world                     # whole-job queries per step (all ranks)
+        flops = 2.0 * Qall * self.N * 128
         recall = float((self.plan.idx[:, 0] == self.pos).float().mean())
-        return {"ms_per_step": round(ms, 3), "queries_per_s": round(self.Q / (ms * 1e-3), 1), "Q_per_step": self.Q,
+        return {"ms_per_step": round(ms, 3), "queries_per_s": round(Qall / (ms * 1e-3), 1), "Q_per_step": Qall,
+                "n_gpus": self.world,
                 "N": self.N, "k": self.k, "algorithmic_tflops": round(flops / (ms * 1e-3) / 1e12, 1),
-                "frac_of_tensor_peak": round(flops / (ms * 1e-3) / 1e12 / peaks["tc"], 4),
+                "frac_of_tensor_peak": round(flops / (ms * 1e-3) / 1e12 / peaks["tc"] / self.world, 4),
                 "unproven_queries": int(self.plan.n_unsafe), "top1_is_planted_positive": round(recall, 4),
                 "pclip_launches_per_step": self.ops.launch_count() / (steps + warmup)}
 
@@ -446,6 +454,19 @@ def main():
             torch.cuda.empty_cache()
         out["workloads"] = extras
         out["cpu_baseline"] = w.cpu_sample()
+    elif not args.no_extras:
+        # N > 1: configs[4] with the queries sharded over a replicated bank (pclip.sharded.ShardedTopk "queries" mode:
+        # independent units, no collective).  Every rank runs it; the time is the max over ranks.
+        del w.plan, w.job
+        torch.cuda.empty_cache()
+        try:
+            wl = Topk4M(dist, Q=(1 << 20) // dist.world, q_total=1 << 20)
+            extras = {"topk_4m_query_sharded": wl.report(dist, peaks)}
+            del wl
+        except Exception as e:
+            extras = {"topk_4m_query_sharded": {"error": f"{type(e).__name__}: {e}"[:300]}}
+        out["workloads"] = extras
+        out["cpu_baseline"] = None
     elif dist.rank == 0:
         out["cpu_baseline"] = None
     if dist.rank == 0:
