@@ -948,24 +948,31 @@ __global__ void col_reduce_kernel(const float* __restrict__ colpart, int nrb, in
   colsum[j] = s;
 }
 
-// Column splits so that the CTA count fills whole waves of the SMs (one CTA per SM): 512 row blocks on 148 SMs are
-// 3.46 waves (87 % of the last wave's SM-time used); split in two they are 6.92 (99 %).  A row shard of a multi-GPU run
-// has fewer row blocks than SMs (64 at B = 65 536 on 8 GPUs): there the split count is searched further (9 splits
-// -> 576 CTAs = 3.9 waves) instead of "about two CTAs per SM" (5 splits -> 2.2 waves, a third of the last wave idle).
-static void plan_waves(int64_t row_blocks, int64_t ntiles, int n_sides, int max_split, int* nsplit, int* tps) {
+// Column splits: the CTA count should fill whole waves of the SMs (one CTA per SM) without paying the per-CTA fixed cost
+// too often.  Model: time ~ waves(ns) * (tiles per split + overhead), overhead = the prologue / final epilogue / partial
+// reduction of one CTA in units of one column tile (measured on the rank-local problem of an 8-GPU run,
+// tools/gpu_shard_sweep.py: ~8 tiles for the gradient kernel, ~2 for the forward kernel).  512 row blocks on 148 SMs:
+// 2 splits (6.9 waves of 264 instead of 3.5 waves -> 4 of 520).  A B/8 row shard (64 CTAs): 9 splits (3.9 waves of 65),
+// not "as many as fill the last wave best" (23 splits of 23 tiles measured 20 % slower).
+static void plan_waves(int64_t row_blocks, int64_t ntiles, int n_sides, int max_split, int overhead_tiles, int* nsplit,
+                       int* tps) {
   const int sms = std::max(device_sm_count(), 1);
   const int64_t base = row_blocks * n_sides;
   const int cap = base < sms ? 8 * max_split : max_split;
-  double best = 0.0;
+  int64_t best = -1;
   int best_ns = 1;
   for (int ns = 1; ns <= cap && (ns == 1 || ns * 4 <= ntiles); ++ns) {
     const int64_t t = ceil_div(ntiles, (int64_t)ns);                       // tiles per split
     const int64_t ctas = base * ceil_div(ntiles, t);
-    const double eff = (double)ctas / (double)(ceil_div(ctas, (int64_t)sms) * sms);
-    if (eff > best + 0.02) {
-      best = eff;
+    const int64_t cost = ceil_div(ctas, (int64_t)sms) * (t + overhead_tiles);
+    if (best < 0 || cost < best) {
+      best = cost;
       best_ns = ns;
     }
+  }
+  if (const char* e = getenv("PCLIP_NSPLIT")) {   // tuning override (tools/gpu_shard_sweep.py)
+    const int v = atoi(e);
+    if (v >= 1 && v <= cap && (v == 1 || v * 4 <= ntiles)) best_ns = v;
   }
   *tps = (int)ceil_div(ntiles, (int64_t)best_ns);
   *nsplit = (int)ceil_div(ntiles, (int64_t)*tps);
@@ -973,8 +980,8 @@ static void plan_waves(int64_t row_blocks, int64_t ntiles, int n_sides, int max_
 
 size_t tc2_grad_workspace(int64_t Ma, int64_t Nb) {
   int ns, ns2, tps;
-  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 1, 4, &ns, &tps);
-  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 2, 4, &ns2, &tps);
+  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 1, 4, 8, &ns, &tps);
+  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 2, 4, 8, &ns2, &tps);
   ns = std::max(ns, ns2);
   return ns > 1 ? 2 * align_up((size_t)ns * Ma * c2::kDim * sizeof(float), 1024) + 2048 : 2048;
 }
@@ -993,7 +1000,7 @@ int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale
   }
   const int64_t Ma = sides[0].Ma, Nb = sides[0].Nb;
   int nsplit, tps;
-  plan_waves(ceil_div(Ma, kRows), ceil_div(Nb, kTile), n_sides, 4, &nsplit, &tps);
+  plan_waves(ceil_div(Ma, kRows), ceil_div(Nb, kTile), n_sides, 4, 8, &nsplit, &tps);
   Workspace w(ws, ws_bytes);
   Tc2BwdArgs args;
   CUtensorMap maps[4];
@@ -1062,7 +1069,7 @@ int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale
 }
 
 static void plan_fwd2(int64_t Ma, int64_t Nb, int* nsplit, int* tps) {
-  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 1, 8, nsplit, tps);
+  plan_waves(ceil_div(Ma, c2::kRows), ceil_div(Nb, c2::kTile), 1, 8, 2, nsplit, tps);
 }
 
 size_t tc2_sumexp_workspace(int64_t Ma, int64_t Nb) {
