@@ -94,6 +94,14 @@ __global__ void __launch_bounds__(256) rank_kernel(const float* __restrict__ q, 
 // equal score never displaces an earlier one, so ties resolve to the lower index.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kMaxK = 64;
+constexpr int kMaxLists = 296;   // bank splits of the list-mode pass (a handful of rows: two CTAs per SM scan the bank)
+// ... as long as the per-split partial lists (stride = all Q rows: the live count is only known on the device) stay
+// within this budget; never fewer than the kMaxK splits of the full pass
+constexpr size_t kListPartialBudget = size_t(2) << 30;
+static int list_mode_splits(int64_t Q, int k) {
+  const int64_t fit = (int64_t)(kListPartialBudget / ((size_t)Q * k * (sizeof(int64_t) + sizeof(float))));
+  return (int)std::min<int64_t>(kMaxLists, std::max<int64_t>(kMaxK, fit));
+}
 
 __global__ void __launch_bounds__(256) topk_kernel(const float* __restrict__ q, const float* __restrict__ bank,
                                                    int64_t Q, int64_t N, int D, int k, int tiles_per_split,
@@ -167,7 +175,7 @@ __global__ void topk_merge_kernel(const int64_t* __restrict__ idx_in, const floa
   const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (r >= (qcount ? (int64_t)*qcount : Q)) return;
   const int64_t wr = qlist ? (int64_t)qlist[r] : r;  // where the merged row is written
-  int head[kMaxK];
+  int head[kMaxLists];
   for (int l = 0; l < n_lists; ++l) head[l] = 0;
   for (int p = 0; p < k; ++p) {
     int best = -1;
@@ -216,7 +224,7 @@ using namespace pclip;
 
 size_t pclip::simt_topk_workspace(int64_t Q, int64_t N, int k, bool list_mode) {
   int nsplit, tps;
-  plan_n_split(list_mode ? 64 : Q, N, kMaxK, &nsplit, &tps);
+  plan_n_split(list_mode ? 64 : Q, N, list_mode ? list_mode_splits(Q, k) : kMaxK, &nsplit, &tps);
   if (nsplit == 1 && !list_mode) return 0;
   return align_up((size_t)nsplit * Q * k * sizeof(int64_t), 1024) + align_up((size_t)nsplit * Q * k * sizeof(float), 1024) +
          4096;
@@ -227,7 +235,7 @@ int pclip::simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, in
                      const int32_t* qcount) {
   int nsplit, tps;
   // list mode: the number of live rows is only known on the device; plan the bank split for a handful of rows
-  plan_n_split(qlist ? 64 : Q, N, kMaxK, &nsplit, &tps);
+  plan_n_split(qlist ? 64 : Q, N, qlist ? list_mode_splits(Q, k) : kMaxK, &nsplit, &tps);
   int64_t* pidx = idx;
   float* pscore = score;
   if (nsplit > 1 || qlist) {
