@@ -32,8 +32,8 @@ constexpr int kStages = 3;              // bank ring
 constexpr int kMaxCand = 32;            // candidate list capacity per query
 constexpr int kThreads = 64 + 32 * 4 * kQTiles;  // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kEpiThreadsPerTile = 128;
-// smem: A (2 tiles) | B ring | candidate scores [kMaxCand][256] | candidate idx [kMaxCand][256] | barriers
-constexpr uint32_t kSmemBytes = kTileBytes * (kQTiles + kStages) + kMaxCand * kRows * 8 + 256 + 1024;
+// smem: A (2 tiles) | B ring | barriers
+constexpr uint32_t kSmemBytes = kTileBytes * (kQTiles + kStages) + 256 + 1024;
 static_assert(kSmemBytes <= 232448, "shared memory budget");
 
 // K-major tile descriptor, built once per tile and advanced per k-step by a constant (ptx.cuh desc_advance)
@@ -87,6 +87,20 @@ struct TopkArgs {
   float* cand_score;    // [nsplit][Q][kc]   bf16-path score
 };
 
+// r[e] for a runtime e without spilling r to local memory: a 5-level select tree
+__device__ __forceinline__ float sel32(const uint32_t (&r)[32], int e) {
+  uint32_t a[16], b[8], c[4];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = (e & 1) ? r[2 * i + 1] : r[2 * i];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) b[i] = (e & 2) ? a[2 * i + 1] : a[2 * i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) c[i] = (e & 4) ? b[2 * i + 1] : b[2 * i];
+  const uint32_t d0 = (e & 8) ? c[1] : c[0], d1 = (e & 8) ? c[3] : c[2];
+  return __uint_as_float((e & 16) ? d1 : d0);
+}
+
+template <int KC>
 __global__ void __launch_bounds__(tk::kThreads, 1)
 tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tb, const TopkArgs args) {
   using namespace tk;
@@ -100,9 +114,7 @@ tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_tiles = smem;
   uint8_t* b_tiles = a_tiles + kQTiles * kTileBytes;
-  float* ls = reinterpret_cast<float*>(b_tiles + kStages * kTileBytes);   // [kMaxCand][kRows]
-  int32_t* li = reinterpret_cast<int32_t*>(ls + kMaxCand * kRows);        // [kMaxCand][kRows]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(li + kMaxCand * kRows);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(b_tiles + kStages * kTileBytes);
   uint64_t* a_full = bars;                       // 1
   uint64_t* b_full = a_full + 1;                 // kStages
   uint64_t* b_empty = b_full + kStages;          // kStages
@@ -180,15 +192,17 @@ tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
       }
     }
   } else {
-    // ---- epilogue: thread == query row; candidate list columns of shared memory are private to the thread ----
+    // ---- epilogue: thread == query row; its sorted candidate list (KC scores + bank rows) lives in registers ----
     const int h = (warp - 2) >> 2;   // query tile
     const int q = warp & 3;          // TMEM lane quadrant this warp may read
     const int lrow = h * kTile + q * 32 + lane;
-    float* my_s = ls + lrow;         // element j at my_s[j * kRows]
-    int32_t* my_i = li + lrow;
-    const int kc = args.kc;
-    int cnt = 0;
-    float thr = -FLT_MAX;            // kc-th best so far once the list is full
+    float cs[KC];                    // descending; -inf = empty slot
+    int32_t ci[KC];
+#pragma unroll
+    for (int j = 0; j < KC; ++j) {
+      cs[j] = -INFINITY;
+      ci[j] = -1;
+    }
     for (int t = 0; t < ntiles; ++t) {
       const int buf = t & 1;
       const uint32_t bphase = (uint32_t)(t >> 1) & 1u;
@@ -210,22 +224,29 @@ tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
         float m = -FLT_MAX;
 #pragma unroll
         for (int e = 0; e < 32; e += 2) m = max3(m, __uint_as_float(r[e]), __uint_as_float(r[e + 1]));
-        if (m > thr || cnt < kc) {
+        if (m > cs[KC - 1]) {
+          uint32_t hits = 0;   // elements above the threshold as of now; re-checked at insert time
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const float v = __uint_as_float(r[e]);
-            if ((v > thr || cnt < kc) && v > -FLT_MAX) {
-              // sorted insert (descending); an equal score stays behind earlier (lower-index) entries
-              int p = cnt < kc ? cnt : kc - 1;
-              while (p > 0 && my_s[(p - 1) * kRows] < v) {
-                my_s[p * kRows] = my_s[(p - 1) * kRows];
-                my_i[p * kRows] = my_i[(p - 1) * kRows];
-                --p;
+          for (int e = 0; e < 32; ++e) hits |= (__uint_as_float(r[e]) > cs[KC - 1] ? 1u : 0u) << e;
+#pragma unroll 1
+          for (; hits; hits &= hits - 1) {   // ascending e: equal scores keep bank order
+            const int e = __ffs(hits) - 1;
+            const float v = sel32(r, e);
+            if (v > cs[KC - 1] && v > -FLT_MAX) {
+              // sorted insert (descending) as a branch-free shift chain over the register list; an equal score stays
+              // behind earlier (lower-index) entries
+              const int32_t id = (int32_t)(col0 + c * 32 + e);
+#pragma unroll
+              for (int j = KC - 1; j >= 1; --j) {
+                const bool shift = cs[j - 1] < v;
+                const bool here = !shift && cs[j] < v;
+                cs[j] = shift ? cs[j - 1] : (here ? v : cs[j]);
+                ci[j] = shift ? ci[j - 1] : (here ? id : ci[j]);
               }
-              my_s[p * kRows] = v;
-              my_i[p * kRows] = (int32_t)(col0 + c * 32 + e);
-              if (cnt < kc) ++cnt;
-              if (cnt == kc) thr = my_s[(kc - 1) * kRows];
+              if (cs[0] < v) {
+                cs[0] = v;
+                ci[0] = id;
+              }
             }
           }
         }
@@ -235,10 +256,11 @@ tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
     }
     const int64_t row = row0 + lrow;
     if (row < args.Q) {
-      const int64_t o = ((int64_t)blockIdx.y * args.Q + row) * kc;
-      for (int j = 0; j < kc; ++j) {
-        args.cand_idx[o + j] = j < cnt ? my_i[j * kRows] : -1;
-        args.cand_score[o + j] = j < cnt ? my_s[j * kRows] : -FLT_MAX;
+      const int64_t o = ((int64_t)blockIdx.y * args.Q + row) * KC;
+#pragma unroll
+      for (int j = 0; j < KC; ++j) {
+        args.cand_idx[o + j] = ci[j];
+        args.cand_score[o + j] = ci[j] >= 0 ? cs[j] : -FLT_MAX;
       }
     }
   }
@@ -342,7 +364,8 @@ topk_rescore_kernel(const float* __restrict__ q, const float* __restrict__ bank,
 // ---------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------
-static int cand_per_query(int k) { return std::min(tk::kMaxCand, std::max(16, 2 * k + 4)); }
+// candidates kept per (query, split): >= 2k + 4, rounded up to a list length the kernel is instantiated for
+static int cand_per_query(int k) { return k <= 6 ? 16 : (k <= 10 ? 24 : tk::kMaxCand); }
 
 static void plan_topk_split(int64_t Q, int64_t N, int kc, int* nsplit, int* tps) {
   const int64_t rb = ceil_div(Q, tk::kRows), nt = ceil_div(N, tk::kTile);
@@ -422,10 +445,10 @@ int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int 
   PCLIP_TRY(make_tmap_bf16_2d(&mq, t.qb, (uint64_t)Q, tk::kDim, tk::kDim, tk::kTile, 64));
   PCLIP_TRY(make_tmap_bf16_2d(&mb, t.bb, (uint64_t)N, tk::kDim, tk::kDim, tk::kTile, 64));
   TopkArgs a{Q, N, kc, tps, t.cand_idx, t.cand_score};
-  PCLIP_CHECK_CUDA(
-      cudaFuncSetAttribute(tc_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk::kSmemBytes));
+  auto kern = kc == 16 ? tc_topk_kernel<16> : (kc == 24 ? tc_topk_kernel<24> : tc_topk_kernel<32>);
+  PCLIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk::kSmemBytes));
   dim3 grid((unsigned)ceil_div(Q, tk::kRows), (unsigned)nsplit);
-  tc_topk_kernel<<<grid, tk::kThreads, tk::kSmemBytes, st>>>(mq, mb, a);
+  kern<<<grid, tk::kThreads, tk::kSmemBytes, st>>>(mq, mb, a);
   PCLIP_CHECK_LAUNCH();
   topk_rescore_kernel<<<(unsigned)ceil_div(Q, kRescoreWarps), kRescoreWarps * 32, 0, st>>>(
       q, bank, t.cand_idx, t.cand_score, t.qnorm, t.scalars, Q, nsplit, kc, k, index_base, idx, score, t.unsafe,
