@@ -94,23 +94,40 @@ __global__ void __launch_bounds__(256) rank_kernel(const float* __restrict__ q, 
 // equal score never displaces an earlier one, so ties resolve to the lower index.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kMaxK = 64;
-constexpr int kMaxLists = 296;   // bank splits of the list-mode pass (a handful of rows: two CTAs per SM scan the bank)
-// ... as long as the per-split partial lists (stride = all Q rows: the live count is only known on the device) stay
-// within this budget; never fewer than the kMaxK splits of the full pass
+constexpr int kMaxLists = 296;   // most bank splits of the list-mode pass (a handful of rows: two CTAs per SM scan the bank)
+// List mode: the number of listed rows is only known on the device, so the bank split is chosen there.  The partial
+// lists ([split][listed row][k]) get a fixed budget of entries; a few listed rows use all kMaxLists splits, many rows
+// fewer, longer ones.  (A host-side plan had to assume all Q rows could be listed: 68 splits at Q = 262 144, 18 ms for
+// 3 rows.)
 constexpr size_t kListPartialBudget = size_t(2) << 30;
-static int list_mode_splits(int64_t Q, int k) {
-  const int64_t fit = (int64_t)(kListPartialBudget / ((size_t)Q * k * (sizeof(int64_t) + sizeof(float))));
-  return (int)std::min<int64_t>(kMaxLists, std::max<int64_t>(kMaxK, fit));
+static int64_t list_mode_entries(int64_t Q, int k) {
+  const int64_t budget = (int64_t)(kListPartialBudget / (sizeof(int64_t) + sizeof(float)));
+  return std::max<int64_t>(Q * k, std::min<int64_t>(budget, (int64_t)kMaxLists * Q * k));
+}
+__device__ __forceinline__ void list_mode_plan(int64_t count, int k, int64_t entries, int64_t ntiles, int max_splits,
+                                               int* tps, int* n_used) {
+  int64_t n = entries / (count * k);
+  n = n < 1 ? 1 : (n > max_splits ? max_splits : n);
+  n = n > ntiles ? ntiles : n;
+  *tps = (int)((ntiles + n - 1) / n);
+  *n_used = (int)((ntiles + *tps - 1) / *tps);
 }
 
 __global__ void __launch_bounds__(256) topk_kernel(const float* __restrict__ q, const float* __restrict__ bank,
                                                    int64_t Q, int64_t N, int D, int k, int tiles_per_split,
                                                    int64_t index_base, int64_t* __restrict__ idx_out,
                                                    float* __restrict__ score_out, const int32_t* __restrict__ qlist,
-                                                   const int32_t* __restrict__ qcount) {
+                                                   const int32_t* __restrict__ qcount, int64_t list_entries) {
   // list mode (qlist != NULL): logical row r is query qlist[r]; only the first *qcount logical rows exist.
-  const int64_t Qstride = Q;
-  if (qcount) Q = *qcount;
+  int64_t Qstride = Q;
+  if (qcount) {
+    Q = *qcount;
+    if (Q <= 0) return;
+    int n_used;
+    list_mode_plan(Q, k, list_entries, ceil_div(N, kBN), (int)gridDim.y, &tiles_per_split, &n_used);
+    if ((int)blockIdx.y >= n_used) return;
+    Qstride = Q;
+  }
   extern __shared__ __align__(16) uint8_t dyn[];
   float(*As)[kBM + kPad] = reinterpret_cast<float(*)[kBM + kPad]>(dyn);
   float(*Bs)[kBN + kPad] = As + kBK;
@@ -171,9 +188,15 @@ __global__ void __launch_bounds__(256) topk_kernel(const float* __restrict__ q, 
 // merge n_lists sorted candidate lists per query: lists laid out [n_lists][Q][k]; (score desc, index asc)
 __global__ void topk_merge_kernel(const int64_t* __restrict__ idx_in, const float* __restrict__ score_in, int64_t Q,
                                   int n_lists, int k, int64_t* __restrict__ idx, float* __restrict__ score,
-                                  const int32_t* __restrict__ qlist, const int32_t* __restrict__ qcount) {
+                                  const int32_t* __restrict__ qlist, const int32_t* __restrict__ qcount,
+                                  int64_t list_entries, int64_t ntiles) {
   const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (r >= (qcount ? (int64_t)*qcount : Q)) return;
+  if (qcount) {   // list mode: the split the scan kernel derived from the live row count
+    Q = *qcount;
+    int tps;
+    list_mode_plan(Q, k, list_entries, ntiles, n_lists, &tps, &n_lists);
+  }
   const int64_t wr = qlist ? (int64_t)qlist[r] : r;  // where the merged row is written
   int head[kMaxLists];
   for (int l = 0; l < n_lists; ++l) head[l] = 0;
@@ -224,10 +247,10 @@ using namespace pclip;
 
 size_t pclip::simt_topk_workspace(int64_t Q, int64_t N, int k, bool list_mode) {
   int nsplit, tps;
-  plan_n_split(list_mode ? 64 : Q, N, list_mode ? list_mode_splits(Q, k) : kMaxK, &nsplit, &tps);
+  plan_n_split(list_mode ? 64 : Q, N, list_mode ? kMaxLists : kMaxK, &nsplit, &tps);
   if (nsplit == 1 && !list_mode) return 0;
-  return align_up((size_t)nsplit * Q * k * sizeof(int64_t), 1024) + align_up((size_t)nsplit * Q * k * sizeof(float), 1024) +
-         4096;
+  const size_t entries = list_mode ? (size_t)list_mode_entries(Q, k) : (size_t)nsplit * Q * k;
+  return align_up(entries * sizeof(int64_t), 1024) + align_up(entries * sizeof(float), 1024) + 4096;
 }
 
 int pclip::simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base,
@@ -235,25 +258,26 @@ int pclip::simt_topk(const float* q, const float* bank, int64_t Q, int64_t N, in
                      const int32_t* qcount) {
   int nsplit, tps;
   // list mode: the number of live rows is only known on the device; plan the bank split for a handful of rows
-  plan_n_split(qlist ? 64 : Q, N, qlist ? list_mode_splits(Q, k) : kMaxK, &nsplit, &tps);
+  plan_n_split(qlist ? 64 : Q, N, qlist ? kMaxLists : kMaxK, &nsplit, &tps);
+  const int64_t entries = qlist ? list_mode_entries(Q, k) : (int64_t)nsplit * Q * k;
   int64_t* pidx = idx;
   float* pscore = score;
   if (nsplit > 1 || qlist) {
     Workspace w(ws, ws_bytes);
     PCLIP_REQUIRE(ws, PCLIP_ERR_WORKSPACE, "topk: workspace required");
-    pidx = w.take<int64_t>((size_t)nsplit * Q * k);
-    pscore = w.take<float>((size_t)nsplit * Q * k);
+    pidx = w.take<int64_t>((size_t)entries);
+    pscore = w.take<float>((size_t)entries);
     PCLIP_REQUIRE(w.ok(), PCLIP_ERR_WORKSPACE, "topk: workspace too small");
   }
   const size_t smem = topk_smem_bytes();
   PCLIP_CHECK_CUDA(cudaFuncSetAttribute(topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t row_blocks = ceil_div(Q, kBM);
   dim3 grid((unsigned)(qlist ? std::min<int64_t>(row_blocks, 8) : row_blocks), (unsigned)nsplit);
-  topk_kernel<<<grid, 256, smem, st>>>(q, bank, Q, N, D, k, tps, index_base, pidx, pscore, qlist, qcount);
+  topk_kernel<<<grid, 256, smem, st>>>(q, bank, Q, N, D, k, tps, index_base, pidx, pscore, qlist, qcount, entries);
   PCLIP_CHECK_LAUNCH();
   if (nsplit > 1 || qlist) {
     topk_merge_kernel<<<(unsigned)ceil_div(Q, 128), 128, 0, st>>>(pidx, pscore, Q, nsplit, k, idx, score, qlist,
-                                                                  qcount);
+                                                                  qcount, entries, ceil_div(N, kBN));
     PCLIP_CHECK_LAUNCH();
   }
   return PCLIP_OK;
@@ -318,7 +342,7 @@ int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, in
   PCLIP_REQUIRE(n_lists >= 1 && n_lists <= kMaxK && k >= 1 && k <= kMaxK, PCLIP_ERR_UNSUPPORTED,
                 "topk_merge: n_lists and k must be in [1, %d]", kMaxK);
   topk_merge_kernel<<<(unsigned)ceil_div(Q, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      idx_in, score_in, Q, n_lists, k, idx, score, nullptr, nullptr);
+      idx_in, score_in, Q, n_lists, k, idx, score, nullptr, nullptr, 0, 0);
   PCLIP_CHECK_LAUNCH();
   return PCLIP_OK;
 }
