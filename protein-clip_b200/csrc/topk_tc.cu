@@ -28,7 +28,7 @@ constexpr uint32_t kPanelBytes = 128 * 128;
 constexpr uint32_t kTileBytes = 2 * kPanelBytes;
 constexpr int kQTiles = 2;              // query tiles per CTA (256 queries): halves the bank traffic per score
 constexpr int kRows = kQTiles * kTile;
-constexpr int kStages = 3;              // bank ring
+constexpr int kStages = 5;              // bank ring
 constexpr int kMaxCand = 32;            // candidate list capacity per query
 constexpr int kThreads = 64 + 32 * 4 * kQTiles;  // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kEpiThreadsPerTile = 128;
