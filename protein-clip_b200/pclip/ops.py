@@ -98,8 +98,9 @@ def clip_loss_raw(xs, ys, compute: int, want_grad: bool, want_lse: bool = False)
     nbytes = lib.pclip_clip_workspace_bytes(B, D, compute)
     owner, ws = L.workspace(nbytes, dev)
     loss = torch.empty(1, dtype=torch.float32, device=dev)
-    dx = torch.empty(B, D, dtype=torch.float32, device=dev) if want_grad else None
-    dy = torch.empty(B, D, dtype=torch.float32, device=dev) if want_grad else None
+    # one allocation for both gradients: backward scales it by grad_output with a single launch
+    dxy = torch.empty(2, B, D, dtype=torch.float32, device=dev) if want_grad else None
+    dx, dy = (dxy[0], dxy[1]) if want_grad else (None, None)
     rl = torch.empty(B, dtype=torch.float32, device=dev) if want_lse else None
     cl = torch.empty(B, dtype=torch.float32, device=dev) if want_lse else None
     with torch.cuda.device(dev):
@@ -119,33 +120,24 @@ class _ClipInfoNCE(torch.autograd.Function):
     def forward(ctx, nx, compute, *tensors):
         xs, ys = list(tensors[:nx]), list(tensors[nx:])
         need = any(t.requires_grad for t in tensors)
-        loss, dx, dy, _, _ = clip_loss_raw([t.detach() for t in xs], [t.detach() for t in ys], compute, need)
+        # grad mode is off inside forward and only the data pointers are read: no per-leaf detach
+        loss, dx, dy, _, _ = clip_loss_raw(xs, ys, compute, need)
         ctx.nx = nx
         ctx.rows = [t.shape[0] for t in tensors]
         ctx.dtypes = [t.dtype for t in tensors]
         if need:
-            ctx.save_for_backward(dx, dy)
+            ctx.save_for_backward(dx._base)         # the [2, B, D] buffer dx and dy are views of
         return loss.reshape(())
 
     @staticmethod
     def backward(ctx, g):
-        dx, dy = ctx.saved_tensors
+        (dxy,) = ctx.saved_tensors                      # [2, B, D] for grad_output == 1
         g = g.reshape(1).float().contiguous()
-        lib = L.lib()
-        outs = []
-        for src in (dx, dy):
-            o = torch.empty_like(src)
-            L.check(lib.pclip_scale_by_scalar(L.ptr(src), L.ptr(g), src.numel(), L.ptr(o), L.stream_ptr(src.device)))
-            outs.append(o)
-        grads = []
-        r = 0
-        for i, n in enumerate(ctx.rows):
-            if i == ctx.nx:
-                r = 0
-            src = outs[0] if i < ctx.nx else outs[1]
-            piece = src[r:r + n]
-            grads.append(piece if ctx.dtypes[i] == torch.float32 else piece.to(ctx.dtypes[i]))
-            r += n
+        out = torch.empty_like(dxy)
+        L.check(L.lib().pclip_scale_by_scalar(L.ptr(dxy), L.ptr(g), dxy.numel(), L.ptr(out), L.stream_ptr(dxy.device)))
+        # the 2B rows in leaf order: x chunks then y chunks
+        pieces = out.view(-1, out.shape[-1]).split(ctx.rows)
+        grads = [p if dt == torch.float32 else p.to(dt) for p, dt in zip(pieces, ctx.dtypes)]
         return (None, None, *grads)
 
 
