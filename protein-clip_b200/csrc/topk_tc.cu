@@ -7,7 +7,8 @@
 //   2. tc_topk_kernel        each CTA keeps 256 queries resident (two 128-row UMMA A tiles), streams the bank through a
 //                            TMA ring, scores 128-column tiles with tcgen05.mma into four TMEM accumulators
 //                            (2 query tiles x double buffer) and filters them in the epilogue: thread == query row,
-//                            register threshold, sorted candidate list (kc >= k + margin entries) in shared memory.
+//                            sorted candidate list (KC >= 2k + 4 entries: 16, 24 or 32) held in the thread's registers,
+//                            its tail is the filter threshold.
 //   3. topk_rescore_kernel   candidates are re-scored with the fp32 FFMA chain of the exact path (bit-identical to
 //                            PCLIP_COMPUTE_F32), sorted (score desc, index asc) and cut to k.  A query is PROVEN exact
 //                            when its k-th fp32 score exceeds (largest discarded bf16 score + eps_q), eps_q being a
