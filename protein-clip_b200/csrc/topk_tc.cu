@@ -368,12 +368,23 @@ topk_rescore_kernel(const float* __restrict__ q, const float* __restrict__ bank,
 // candidates kept per (query, split): >= 2k + 4, rounded up to a list length the kernel is instantiated for
 static int cand_per_query(int k) { return k <= 6 ? 16 : (k <= 10 ? 24 : tk::kMaxCand); }
 
+// Bank splits: fill whole waves of the SMs (one CTA per SM).  Cost model as for the CLIP kernels: waves x (tiles per
+// split + overhead), overhead = a CTA's start-up phase (lists still filling, most tiles insert) in units of one bank
+// tile.  512 query blocks (131 072 queries): 2 splits = 6.9 waves of 16 384 tiles instead of 3.5 -> 4 waves of 32 768.
 static void plan_topk_split(int64_t Q, int64_t N, int kc, int* nsplit, int* tps) {
   const int64_t rb = ceil_div(Q, tk::kRows), nt = ceil_div(N, tk::kTile);
-  int64_t want = ceil_div(148, rb);
-  want = std::min<int64_t>(want, kMaxCandTotal / kc);
-  want = std::max<int64_t>(1, std::min(want, nt));
-  *tps = (int)ceil_div(nt, want);
+  const int64_t sms = 148, overhead = 128;
+  const int64_t max_ns = std::max<int64_t>(1, std::min<int64_t>(kMaxCandTotal / kc, nt));
+  int64_t best_ns = 1, best_cost = -1;
+  for (int64_t ns = 1; ns <= max_ns; ++ns) {
+    const int64_t t = ceil_div(nt, ns);
+    const int64_t cost = ceil_div(rb * ceil_div(nt, t), sms) * (t + overhead);
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best_ns = ns;
+    }
+  }
+  *tps = (int)ceil_div(nt, best_ns);
   *nsplit = (int)ceil_div(nt, *tps);
 }
 
