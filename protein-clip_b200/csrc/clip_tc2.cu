@@ -18,7 +18,7 @@
 #include "ptx.cuh"
 
 #ifndef PCLIP_FWD_POLY
-#define PCLIP_FWD_POLY 14
+#define PCLIP_FWD_POLY 10
 #endif
 #ifndef PCLIP_BWD_POLY
 #define PCLIP_BWD_POLY 8
@@ -648,10 +648,12 @@ tc3_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__
 // CTA = 256 rows (two 128-row A tiles share every streamed column tile: the kernel was bound by the L2 -> SMEM
 // latency of the column tiles with 128-row CTAs, profiles/r01c).  Work items u = (column tile t, row half h).
 //   warp 0      TMA producer (A tiles once, column-tile ring)
-//   warp 1      MMA issuer: S(u) = A_h Y_t^T into one of three TMEM accumulators, and the column-sum MMA
-//               C_t += E(u)^T . ones (M = 128 columns, N = 16, the bf16 exp tile is the MN-major A operand).  It polls
-//               its barriers so that a column-sum MMA never queues behind a wait for a column tile still in flight.
-//   warps 2-17  epilogue: 4 lane quadrants x 4 column quarters; thread = one row x 32 columns of the item.
+//   warp 1      score-MMA issuer: S(u) = A_h Y_t^T into one of three TMEM accumulators, up to three items ahead
+//   warps 2-17  epilogue, eight warps per row half (4 lane quadrants x 2 column halves): thread = one row x 64 columns
+//               of its half's item, two 32-column TMEM loads; the two halves' items are processed side by side
+//   warp 18     column-sum MMA issuer: C_t += E(u)^T . ones (M = 128 columns, N = 16, the bf16 exp tile is the
+//               MN-major A operand) as soon as item u's exp tile is complete -- in one issue loop with the score
+//               MMAs each waited on the other's barriers
 // =================================================================================================================
 struct Tc2FwdArgs {
   int64_t Ma, Nb, diag_offset;
@@ -676,7 +678,7 @@ constexpr uint32_t kFwdSmem = kTileBytes * (kH + kFwdStages + kEBuf) + kOnesByte
 static_assert(kFwdSmem <= 232448, "shared memory budget");
 constexpr int kFwdPoly = PCLIP_FWD_POLY;  // of every 32 exps, this many on the FMA pipes (degree 4)
 constexpr int kFwdEpiWarps = 16;          // 4 warps per SM sub-partition
-constexpr int kFwdThreads = 64 + 32 * kFwdEpiWarps;
+constexpr int kFwdThreads = 64 + 32 * kFwdEpiWarps + 32;   // + the column-sum issuer warp
 }  // namespace c2
 
 template <int kPoly>
@@ -720,10 +722,10 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
     }
     for (int i = 0; i < kSBuf; ++i) {
       mbar_init(&s_full[i], 1);
-      mbar_init(&s_empty[i], 32 * kFwdEpiWarps);
+      mbar_init(&s_empty[i], 16 * kFwdEpiWarps);   // the eight warps of the item's row half
     }
     for (int i = 0; i < kEBuf; ++i) {
-      mbar_init(&e_full[i], 32 * kFwdEpiWarps);
+      mbar_init(&e_full[i], 16 * kFwdEpiWarps);
       mbar_init(&e_empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
@@ -763,14 +765,10 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
   } else if (warp == 1) {
     if (ntiles > 0) {   // the whole warp runs the issue loop; one elected lane issues each tcgen05 instruction
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, 0, 0);  // S = A . Y^T
-      constexpr uint32_t idesc_c = make_idesc_bf16(kTile, 16, 1, 0);     // C[col, :] = sum_rows E[row, col] (E^T . ones)
-      const uint64_t od = kmajor_base(smem_u32(ones));
       const int n_items = ntiles * nh;
       mbar_wait(a_full, 0);
-      // Fixed issue order with blocking waits: S runs kSBuf items ahead; the column sums of item u go out as soon as
-      // its exp tile is complete, followed by the score MMA that reuses the accumulator item u released long before.
-      // (A polling loop here lost ~1000 clk per item: the issuing thread shares its scheduler with four epilogue
-      // warps and was starved while they were busy, profiles/r01c fwd trace.)
+      // Score MMAs run up to kSBuf items ahead of the epilogue, with blocking waits (a polling loop lost ~1000 clk per
+      // item: the issuing thread shares its scheduler with four epilogue warps and was starved while they were busy).
       auto issue_s = [&](int u) {
         const int t = u / nh, h = u - t * nh;
         const int sb = u % kSBuf, stage = t % kFwdStages;
@@ -790,7 +788,13 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
         __syncwarp();
         if (lane == 0) PCLIP_TRACE(7, u);
       };
-      for (int u = 0; u < min(kSBuf, n_items); ++u) issue_s(u);
+      for (int u = 0; u < n_items; ++u) issue_s(u);
+    }
+  } else if (warp == 2 + kFwdEpiWarps) {
+    if (ntiles > 0) {   // column-sum issuer: its own warp, so that a wait for an exp tile never holds back the score MMAs
+      constexpr uint32_t idesc_c = make_idesc_bf16(kTile, 16, 1, 0);     // C[col, :] = sum_rows E[row, col] (E^T . ones)
+      const uint64_t od = kmajor_base(smem_u32(ones));
+      const int n_items = ntiles * nh;
       for (int u = 0; u < n_items; ++u) {
         const int t = u / nh, h = u - t * nh;
         const int eb = u % kEBuf;
@@ -809,17 +813,22 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
         }
         __syncwarp();
         if (lane == 0) PCLIP_TRACE(0, u);
-        if (u + kSBuf < n_items) issue_s(u + kSBuf);
       }
     }
-  } else {
-    const int quarter = (warp - 2) >> 2, q = warp & 3;                // 32 columns of 32 rows per warp and item
+  } else if (warp < 2 + kFwdEpiWarps) {
+    // Eight warps per row half: warp = (row half, 64-column half, lane quadrant); thread = one row x 64 columns of its
+    // half's item, read as two 32-column TMEM loads.  The two halves' items are in flight side by side, and the
+    // per-item barrier / store / fence overhead is paid once per 64 columns instead of once per 32.
+    const int w = warp - 2;
+    const int grp = w >> 3;                  // row half this warp serves: items u = t * nh + grp
+    const int colhalf = (w >> 2) & 1;        // columns [64 * colhalf, +64) of the item == K panel of the exp tile
+    const int q = warp & 3;                  // TMEM lane quadrant this warp may read
     const int i = q * 32 + lane;
-    float rs[2] = {0.f, 0.f}, dval[2] = {0.f, 0.f};
-    bool dfound[2] = {false, false};
+    float rsum = 0.f, dval = 0.f;
+    bool dfound = false;
     float* colpart = args.colpart + (int64_t)blockIdx.x * args.Nb;
     const uint32_t e_base = smem_u32(e_tiles);
-    auto flush_cols = [&](int t) {   // column sums of tile t: TMEM lane == column; read by the quarter-0 warps
+    auto flush_cols = [&](int t) {   // column sums of tile t: TMEM lane == column; read by four warps of row half 0
       const int buf = t & 1;
       mbar_wait(&c_full[buf], (uint32_t)(t >> 1) & 1u);
       tc_fence_after_sync();
@@ -832,28 +841,36 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
       tc_fence_before_sync();
       mbar_arrive(&c_empty[buf]);
     };
-    int sb = 0, eb = 0;
-    uint32_t sph = 0, eph = 0;
-    for (int t = 0; t < ntiles; ++t) {
-      const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
+    if (grp < nh) {
+      const int h = grp;
+      const bool flusher = grp == 0 && colhalf == 0;
+      const int64_t rb = row0 + h * kTile;                          // first row of this half
+      const int64_t row = rb + i;
+      const int64_t drow = args.diag_offset + row;                  // my positive's column
+      const int64_t dlo = args.diag_offset + rb, dhi = dlo + kTile; // diagonal band of this half
+      const bool row_ragged = rb + kTile > args.Ma;
+      for (int t = 0; t < ntiles; ++t) {
+        const int u = t * nh + h;
+        const int sb = u % kSBuf, eb = u % kEBuf;
+        const uint32_t sph = (uint32_t)(u / kSBuf) & 1u, eph = (uint32_t)(u / kEBuf) & 1u;
+        const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
+        const bool special = row_ragged || (col0 + kTile > args.Nb) || (col0 < dhi && col0 + kTile > dlo);
+        mbar_wait(&e_empty[eb], eph ^ 1u);   // the column-sum MMA of item u - kEBuf has consumed this buffer
+        mbar_wait(&s_full[sb], sph);
+        tc_fence_after_sync();
+        if (threadIdx.x == 64) PCLIP_TRACE(3, u);
+        const uint32_t panel = e_base + (uint32_t)eb * kTileBytes + (uint32_t)colhalf * kPanelBytes;
 #pragma unroll
-      for (int h = 0; h < kH; ++h) {
-        if (h < nh) {
-          const int64_t rb = row0 + h * kTile;                          // first row of this half
-          const int64_t row = rb + i;
-          const int64_t drow = args.diag_offset + row;                  // my positive's column
-          const int64_t dlo = args.diag_offset + rb, dhi = dlo + kTile; // diagonal band of this half
-          const bool special = (rb + kTile > args.Ma) || (col0 + kTile > args.Nb) || (col0 < dhi && col0 + kTile > dlo);
-          mbar_wait(&s_full[sb], sph);
-          tc_fence_after_sync();
-          if (threadIdx.x == 64) PCLIP_TRACE(3, t * nh + h);
+        for (int c = 0; c < 2; ++c) {
           uint32_t v[32];
-          tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)sb * kTile + (uint32_t)quarter * 32u, v);
+          tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)sb * kTile +
+                                 (uint32_t)(colhalf * 64 + c * 32), v);
           tmem_ld_wait();
-          tc_fence_before_sync();
-          mbar_arrive(&s_empty[sb]);                // S(u) is in registers: the MMA warp may overwrite the accumulator
-          if (threadIdx.x == 64) PCLIP_TRACE(4, t * nh + h);
-          if (++sb == kSBuf) { sb = 0; sph ^= 1u; }
+          if (c == 1) {
+            tc_fence_before_sync();
+            mbar_arrive(&s_empty[sb]);              // S(u) is in registers: the MMA warp may overwrite the accumulator
+            if (threadIdx.x == 64) PCLIP_TRACE(4, u);
+          }
           uint32_t packed[16];
           if (!special) {
             uint64_t acc = pack2(0.f, 0.f);
@@ -873,50 +890,44 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
             }
             float a0, a1;
             unpack2(acc, a0, a1);
-            rs[h] += a0 + a1;
+            rsum += a0 + a1;
           } else {
 #pragma unroll
             for (int e = 0; e < 32; e += 2) {
               float ev[2];
 #pragma unroll
-              for (int u = 0; u < 2; ++u) {
-                const int64_t col = col0 + quarter * 32 + e + u;
-                const float sv = __uint_as_float(v[e + u]);
+              for (int k2 = 0; k2 < 2; ++k2) {
+                const int64_t col = col0 + colhalf * 64 + c * 32 + e + k2;
+                const float sv = __uint_as_float(v[e + k2]);
                 float x = (col < args.Nb && row < args.Ma) ? ex2_approx(sv * kLog2e) : 0.f;
-                if (col < args.Nb) rs[h] += x;
+                if (col < args.Nb) rsum += x;
                 if (col == drow) {       // keep the positive out of the bf16 column sum: col_reduce adds it in fp32
-                  dval[h] = sv;
-                  dfound[h] = true;
+                  dval = sv;
+                  dfound = true;
                   x = 0.f;
                 }
-                ev[u] = x;
+                ev[k2] = x;
               }
               packed[e >> 1] = bf16x2_bits(ev[0], ev[1]);
             }
           }
-          if (threadIdx.x == 64) PCLIP_TRACE(5, t * nh + h);
-          mbar_wait(&e_empty[eb], eph ^ 1u);   // the column-sum MMA of item u - kEBuf has consumed this buffer
-          const uint32_t panel = e_base + (uint32_t)eb * kTileBytes + (uint32_t)(quarter >> 1) * kPanelBytes;
 #pragma unroll
           for (int g = 0; g < 4; ++g)
-            st_shared_v4(panel + sw128_offset((uint32_t)i, (uint32_t)((quarter & 1) * 4 + g)), packed[4 * g],
-                         packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
-          fence_proxy_async_smem();
-          mbar_arrive(&e_full[eb]);
-          if (threadIdx.x == 64) PCLIP_TRACE(6, t * nh + h);
-          if (++eb == kEBuf) { eb = 0; eph ^= 1u; }
+            st_shared_v4(panel + sw128_offset((uint32_t)i, (uint32_t)(c * 4 + g)), packed[4 * g], packed[4 * g + 1],
+                         packed[4 * g + 2], packed[4 * g + 3]);
         }
+        if (threadIdx.x == 64) PCLIP_TRACE(5, u);
+        fence_proxy_async_smem();
+        mbar_arrive(&e_full[eb]);
+        if (threadIdx.x == 64) PCLIP_TRACE(6, u);
+        if (flusher && t > 0) flush_cols(t - 1);   // one tile behind: never waits on the MMA just requested
       }
-      if (quarter == 0 && t > 0) flush_cols(t - 1);   // one tile behind: never waits on the MMA just requested
-    }
-    if (quarter == 0 && ntiles > 0) flush_cols(ntiles - 1);
-    // row sums: one partial per (split, column quarter)
-#pragma unroll
-    for (int h = 0; h < kH; ++h) {
-      const int64_t row = row0 + h * kTile + i;
-      if (h < nh && row < args.Ma) {
-        args.rowpart[((int64_t)blockIdx.y * 4 + quarter) * args.Ma + row] = rs[h];
-        if (dfound[h]) args.diag[row] = dval[h];
+      if (flusher && ntiles > 0) flush_cols(ntiles - 1);
+      // row sums: one partial per (split, column quarter); this thread covered two quarters
+      if (row < args.Ma) {
+        args.rowpart[((int64_t)blockIdx.y * 4 + colhalf * 2) * args.Ma + row] = rsum;
+        args.rowpart[((int64_t)blockIdx.y * 4 + colhalf * 2 + 1) * args.Ma + row] = 0.f;
+        if (dfound) args.diag[row] = dval;
       }
     }
   }
@@ -1114,7 +1125,9 @@ int tc2_sumexp(const void* a, const void* b, int64_t Ma, int64_t Nb, int64_t dia
   } while (0)
   if (poly <= 0) PCLIP_LAUNCH_FWD(0);
   else if (poly <= 6) PCLIP_LAUNCH_FWD(6);
+  else if (poly <= 8) PCLIP_LAUNCH_FWD(8);
   else if (poly <= 10) PCLIP_LAUNCH_FWD(10);
+  else if (poly <= 12) PCLIP_LAUNCH_FWD(12);
   else if (poly <= 14) PCLIP_LAUNCH_FWD(14);
   else PCLIP_LAUNCH_FWD(18);
 #undef PCLIP_LAUNCH_FWD

@@ -5,7 +5,7 @@ python -m pytest tests -m gpu -x -q > gpurun_out/tests.log 2>&1; echo "tests exi
 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" >> gpurun_out/smoke.log
 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?" >> gpurun_out/bench.err
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2>&1
-KPAT=${KPAT:-tc2_grad_kernel}
+KPAT=${KPAT:-tc3_grad_kernel}
 python bench.py --steps 2 --warmup 1 --no-extras > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 1 --no-extras > gpurun_out/ncu1.log 2>&1
