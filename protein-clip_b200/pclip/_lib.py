@@ -6,6 +6,7 @@ with a clear message (build it with `make` at the repo root or `python -c "impor
 from __future__ import annotations
 
 import ctypes as C
+import struct
 import os
 
 import torch
@@ -122,11 +123,13 @@ def dtype_code(dt: torch.dtype) -> int:
 
 
 def chunks_of(tensors) -> "C.Array[Chunk]":
-    arr = (Chunk * len(tensors))()
-    for i, t in enumerate(tensors):
+    # one packed buffer instead of a ctypes Structure per tensor: this runs once per leaf on the GradCache path
+    flat = []
+    for t in tensors:
         assert t.dim() == 2
-        arr[i] = Chunk(t.data_ptr(), t.shape[0], t.stride(0), t.stride(1))
-    return arr
+        st = t.stride()
+        flat += (t.data_ptr(), t.shape[0], st[0], st[1])
+    return (Chunk * len(tensors)).from_buffer_copy(struct.pack(f"{len(flat)}q", *flat))
 
 
 def require_cuda(*tensors):
