@@ -244,8 +244,8 @@ class ClipLarge:
         return {"bound": "tensor", "kernel": "tc3_grad_kernel", "achieved": round(ach, 1), "peak": peaks["tc"],
                 "unit": "TFLOP/s", "frac": round(ach / peaks["tc"], 4),
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch at B = 65 536 on one GPU
-                # (profiles/r01d_tc3_grad_kernel_ncu_full.txt); algorithmic bytes: 2 B D (2 + 4) = 100.7 MB
-                "traffic": 132.5e6 if (Ma == B and B == 65536) else None,
+                # (profiles/r01g_tc3_grad_kernel_ncu_full.txt: 49.8 + 82.4 MB); algorithmic bytes: 2 B D (2 + 4) = 100.7 MB
+                "traffic": 132.1e6 if (Ma == B and B == 65536) else None,
                 "peak_source": f"{peaks['src']} bf16_tflops_sustained",
                 "algorithmic_flops_per_launch": flops, "kernel_ms": round(out["grad"], 4),
                 "other_kernels_ms": {"tc2_sumexp_kernel (+2 small reduces)": round(out["rowsumexp"], 4)}}
