@@ -3,16 +3,13 @@
 // The reference materialises S[1,1,Ba,Bb,TA,TB] (64 GiB at B = 256, T = 512) three times over; here a score tile lives
 // only in TMEM.
 //
-//   filip_prep_kernel      fp32 tokens -> bf16 rows [B,T,128] (fwd operands) and bf16 transposed [B,128,Tld] (bwd B
-//                          operand), pads zeroed
+//   filip_prep_kernel      fp32 tokens -> bf16 rows [B,T,128] (forward operands; the backward gathers the same rows),
+//                          pads zeroed
 //   tc_filip_max_kernel    one "side" (see filip.cu): CTA = 256 tokens of one sample (two UMMA row tiles sharing the
 //                          streamed column tiles), TMA ring -> tcgen05.mma -> 4 TMEM accumulators; epilogue thread ==
 //                          token row keeps the running max / argmax over the column sample's tokens in registers,
 //                          applies the length mask, and emits int16 argmax + per-warp partial sums of the masked mean
-//   tc_filip_grad_kernel   one side of the backward as a tensor-core contraction with a SPARSE ONE-HOT operand:
-//                          dX[x, t, :] = sum_y P_xy[t, :] . Y[y],   P_xy[t, s] = wX [s == argX[x,y,t]] + wY [t == argY[y,x,s]]
-//                          P tiles (<= 256 non-zeros of 16 384) are maintained in shared memory by "builder" warps that
-//                          only touch the non-zeros (set, then clear after the MMA has consumed the tile)
+//   backward               filip_bwd.cu (gather / scatter over the stored argmax indices)
 #include <cuda_bf16.h>
 #include <float.h>
 
@@ -47,38 +44,22 @@ __device__ __forceinline__ void issue_tile(uint32_t d, uint32_t a_addr, uint32_t
 }  // namespace fl
 
 // ---------------------------------------------------------------------------------------------------------
-// prep: grid (ceil(T/32), B), 256 threads
+// prep: one warp per token row (grid-stride), lane = 4 dims
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-filip_prep_kernel(const float* __restrict__ h, const int32_t* __restrict__ len, int T, int64_t Tld,
-                  __nv_bfloat16* __restrict__ rows /* [B,T,128] */, __nv_bfloat16* __restrict__ colsT /* [B,128,Tld] */) {
-  __shared__ float tile[32][129];
-  const int b = blockIdx.y, t0 = blockIdx.x * 32;
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int L = min(len[b], T);
-#pragma unroll
-  for (int rr = 0; rr < 4; ++rr) {
-    const int lr = w * 4 + rr, t = t0 + lr;
+filip_prep_kernel(const float* __restrict__ h, const int32_t* __restrict__ len, int64_t B, int T,
+                  __nv_bfloat16* __restrict__ rows /* [B,T,128] */) {
+  const int lane = threadIdx.x & 31;
+  const int64_t nrow = B * T;
+  for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < nrow; r += (int64_t)gridDim.x * 8) {
+    const int b = (int)(r / T), t = (int)(r - (int64_t)b * T);
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (t < L) v = *reinterpret_cast<const float4*>(h + ((int64_t)b * T + t) * fl::kDim + lane * 4);
-    tile[lr][lane * 4] = v.x;
-    tile[lr][lane * 4 + 1] = v.y;
-    tile[lr][lane * 4 + 2] = v.z;
-    tile[lr][lane * 4 + 3] = v.w;
-    if (t < T) {
-      __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
-      uint2 pk;
-      pk.x = *reinterpret_cast<uint32_t*>(&lo);
-      pk.y = *reinterpret_cast<uint32_t*>(&hi);
-      *reinterpret_cast<uint2*>(rows + ((int64_t)b * T + t) * fl::kDim + lane * 4) = pk;
-    }
-  }
-  __syncthreads();
-  // transposed copy: warp w writes dims w, w+8, ...; lane = token.  Columns up to Tld are written (zeros beyond len).
-  if (t0 + lane < Tld) {
-#pragma unroll 4
-    for (int d = w; d < fl::kDim; d += 8)
-      colsT[((int64_t)b * fl::kDim + d) * Tld + t0 + lane] = __float2bfloat16_rn(tile[lane][d]);
+    if (t < len[b]) v = __ldg(reinterpret_cast<const float4*>(h + r * fl::kDim) + lane);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *(reinterpret_cast<uint2*>(rows + r * fl::kDim) + lane) = pk;
   }
 }
 
@@ -252,224 +233,24 @@ tc_filip_max_kernel(const __grid_constant__ CUtensorMap tx, const __grid_constan
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// backward side: grid (ceil(Tx/256), Bx).  dX[bx, row0 .. row0+256, :] = sum over (by, s-tile) of P . Y
-// ---------------------------------------------------------------------------------------------------------
-struct FilipBwdArgs {
-  int Bx, By, Tx, Ty;
-  const int32_t* lenX;
-  const int32_t* lenY;
-  const float* tau;
-  const float* gX;
-  int64_t gx0, gx1;      // gX[bx * gx0 + by * gx1]
-  const float* gY;
-  int64_t gy0, gy1;      // gY[by * gy0 + bx * gy1]
-  const int16_t* argX;   // [Bx][By][Tx]
-  const int16_t* argY;   // [By][Bx][Ty]
-  float* dX;             // [Bx][Tx][128]
-};
-
-namespace fl {
-constexpr int kBwdStages = 3;
-// P [kH][2] | Y^T ring | gather-column staging [kH][2][128] int16 | barriers
-constexpr uint32_t kBwdSmem = kTileBytes * (2 * kH + kBwdStages) + kH * 2 * kTile * 2 + 256 + 1024;
-static_assert(kBwdSmem <= 232448, "shared memory budget");
-
-__device__ __forceinline__ uint32_t p_elem_off(int row, int col) {
-  return (uint32_t)(col >> 6) * kPanelBytes + sw128_offset((uint32_t)row, (uint32_t)((col & 63) >> 3)) +
-         (uint32_t)(col & 7) * 2u;
-}
-}  // namespace fl
-
-__global__ void __launch_bounds__(fl::kThreads, 1)
-tc_filip_grad_kernel(const __grid_constant__ CUtensorMap tyT, const FilipBwdArgs args) {
-  using namespace fl;
-  const int bx = blockIdx.y;
-  const int row0 = blockIdx.x * kRows;
-  const int lx = min(args.lenX[bx], args.Tx);
-  const int nh = row0 >= lx ? 0 : (row0 + kTile < lx ? 2 : 1);
-
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* p_tiles = smem;                                   // [kH][2]
-  uint8_t* y_tiles = p_tiles + 2 * kH * kTileBytes;          // ring
-  int16_t* gcol_s = reinterpret_cast<int16_t*>(y_tiles + kBwdStages * kTileBytes);  // [kH][2][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(gcol_s + kH * 2 * kTile);
-  uint64_t* y_full = bars;
-  uint64_t* y_empty = y_full + kBwdStages;
-  uint64_t* p_full = y_empty + kBwdStages;   // [kH][2]
-  uint64_t* p_empty = p_full + 2 * kH;       // [kH][2]
-  uint64_t* d_full = p_empty + 2 * kH;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_full + 1);
-
-  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < kBwdStages; ++i) {
-      mbar_init(&y_full[i], 1);
-      mbar_init(&y_empty[i], 1);
-    }
-    for (int i = 0; i < 2 * kH; ++i) {
-      mbar_init(&p_full[i], 128);
-      mbar_init(&p_empty[i], 1);
-    }
-    mbar_init(d_full, 1);
-    fence_mbar_init();
-  }
-  if (warp == 1) tmem_alloc<256>(tmem_slot);
-  tc_fence_before_sync();
-  __syncthreads();
-  tc_fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0) {
-    if (lane == 0 && nh > 0) {
-      tma_prefetch_desc(&tyT);
-      int it = 0;
-      for (int by = 0; by < args.By; ++by) {
-        const int ly = min(args.lenY[by], args.Ty);
-        for (int s0 = 0; s0 < ly; s0 += kTile, ++it) {
-          const int stage = it % kBwdStages;
-          const uint32_t phase = (uint32_t)(it / kBwdStages) & 1u;
-          mbar_wait(&y_empty[stage], phase ^ 1u);
-          mbar_arrive_expect_tx(&y_full[stage], kTileBytes);
-          uint8_t* dst = y_tiles + (size_t)stage * kTileBytes;
-          tma_load_3d(dst, &tyT, &y_full[stage], s0, 0, by);                  // Y^T[by][0:128, s0 : s0+64]
-          tma_load_3d(dst + kPanelBytes, &tyT, &y_full[stage], s0 + 64, 0, by);
-        }
-      }
-    }
-  } else if (warp == 1) {
-    if (nh > 0) {   // whole warp; tcgen05 instructions go out from one elected lane
-      constexpr uint32_t idesc = make_idesc_bf16(kTile, kTile, 0, 0);
-      int it = 0;
-      for (int by = 0; by < args.By; ++by) {
-        const int ly = min(args.lenY[by], args.Ty);
-        for (int s0 = 0; s0 < ly; s0 += kTile, ++it) {
-          const int stage = it % kBwdStages;
-          const uint32_t phase = (uint32_t)(it / kBwdStages) & 1u;
-          const int buf = it & 1;
-          const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
-          mbar_wait(&y_full[stage], phase);
-          const uint32_t y_addr = smem_u32(y_tiles + (size_t)stage * kTileBytes);
-          for (int h = 0; h < nh; ++h) {
-            mbar_wait(&p_full[h * 2 + buf], bphase);
-            tc_fence_after_sync();
-            issue_tile(tmem_base + (uint32_t)h * kTile, smem_u32(p_tiles + (size_t)(h * 2 + buf) * kTileBytes), y_addr,
-                       idesc, it > 0);
-            if (elect_one()) {
-              umma_commit(&p_empty[h * 2 + buf]);
-              if (h == nh - 1) umma_commit(&y_empty[stage]);
-            }
-            __syncwarp();
-          }
-        }
-      }
-      if (elect_one()) umma_commit(d_full);
-      __syncwarp();
-    }
-  } else {
-    // ---- builder + final epilogue: 128 threads per row tile ----
-    const int h = (warp - 2) >> 2, q = warp & 3;
-    const int i = q * 32 + lane;          // my row of the P tile (gather) and my column of the P tile (scatter)
-    const int tbase = row0 + h * kTile;
-    const int t = tbase + i;
-    const bool live = h < nh;
-    int it = 0;
-    if (live) {
-      uint8_t* myp = p_tiles + (size_t)(h * 2) * kTileBytes;
-      // zero both P buffers of this row tile once (64 KB / 128 threads)
-      for (uint32_t o = (uint32_t)i * 16u; o < 2 * kTileBytes; o += 128u * 16u)
-        *reinterpret_cast<uint4*>(myp + o) = make_uint4(0u, 0u, 0u, 0u);
-      int og[2] = {-1, -1}, os[2] = {-1, -1};
-      const float inv_tau = 1.0f / args.tau[0];
-      const float cx = inv_tau / fmaxf((float)lx, 1e-6f);
-      for (int by = 0; by < args.By; ++by) {
-        const int ly = min(args.lenY[by], args.Ty);
-        if (ly <= 0) continue;
-        const float wx = args.gX[bx * args.gx0 + by * args.gx1] * cx;
-        const float wy = args.gY[by * args.gy0 + bx * args.gy1] * inv_tau / fmaxf((float)ly, 1e-6f);
-        const int sX = t < lx ? (int)args.argX[((int64_t)bx * args.By + by) * args.Tx + t] : -1;
-        const int16_t* ay = args.argY + ((int64_t)by * args.Bx + bx) * args.Ty;
-        const uint16_t wx16 = __bfloat16_as_ushort(__float2bfloat16_rn(wx));
-        for (int s0 = 0; s0 < ly; s0 += kTile, ++it) {
-          const int buf = it & 1;
-          const uint32_t bphase = (uint32_t)(it >> 1) & 1u;
-          const int tY = (s0 + i < ly) ? (int)ay[s0 + i] : -1;   // issued before the wait: latency overlaps it
-          uint8_t* P = myp + (size_t)buf * kTileBytes;
-          int16_t* gs = gcol_s + (h * 2 + buf) * kTile;
-          mbar_wait(&p_empty[h * 2 + buf], bphase ^ 1u);
-          // A: clear what I wrote into this buffer two tiles ago
-          if (og[buf] >= 0) *reinterpret_cast<uint16_t*>(P + og[buf]) = 0;
-          if (os[buf] >= 0) *reinterpret_cast<uint16_t*>(P + os[buf]) = 0;
-          const int gcol = (sX >= s0 && sX < s0 + kTile) ? sX - s0 : -1;
-          gs[i] = (int16_t)gcol;
-          named_bar_sync(1 + h, 128);
-          // B: gather entry of my row
-          if (gcol >= 0) {
-            og[buf] = (int)p_elem_off(i, gcol);
-            *reinterpret_cast<uint16_t*>(P + og[buf]) = wx16;
-          } else {
-            og[buf] = -1;
-          }
-          named_bar_sync(1 + h, 128);
-          // C: scatter entry of my column (merged with the gather entry when both hit the same element)
-          const int r = tY - tbase;
-          if (tY >= 0 && r >= 0 && r < kTile) {
-            const float v = wy + (gs[r] == i ? wx : 0.f);
-            os[buf] = (int)p_elem_off(r, i);
-            *reinterpret_cast<uint16_t*>(P + os[buf]) = __bfloat16_as_ushort(__float2bfloat16_rn(v));
-          } else {
-            os[buf] = -1;
-          }
-          fence_proxy_async_smem();
-          mbar_arrive(&p_full[h * 2 + buf]);
-        }
-      }
-      if (it > 0) {
-        mbar_wait(d_full, 0);
-        tc_fence_after_sync();
-      }
-    }
-    // tcgen05.ld is warp-collective (.sync.aligned): every lane loads, only rows t < Tx store
-    if (tbase + q * 32 < args.Tx) {
-      float* dst = args.dX + ((int64_t)bx * args.Tx + t) * kDim;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)h * kTile;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        if (live && it > 0) {
-          tmem_ld_32x32b_x32(taddr + c * 32, r);
-          tmem_ld_wait();
-        } else {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) r[e] = 0u;
-        }
-        if (t < args.Tx) {
-#pragma unroll
-          for (int e = 0; e < 32; e += 4)
-            *reinterpret_cast<float4*>(dst + c * 32 + e) = make_float4(
-                __uint_as_float(r[e]), __uint_as_float(r[e + 1]), __uint_as_float(r[e + 2]), __uint_as_float(r[e + 3]));
-        }
-      }
-    }
-  }
-  tc_fence_before_sync();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after_sync();
-    __syncwarp();
-    tmem_dealloc<256>(tmem_base);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------
-static int64_t tld(int64_t T) { return (int64_t)align_up((size_t)T, 64); }
 static int np_of(int64_t T) { return (int)ceil_div(T, fl::kRows) * fl::kH * 4; }
 
+// filip_bwd.cu
+size_t filip_gather_inv_elems(int64_t Ba, int64_t Bb, int64_t TA, int64_t TB);
+size_t filip_gather_grp_elems(int64_t Ba, int64_t Bb, int64_t TA, int64_t TB);
+int filip_gather_side(const __nv_bfloat16* Yr, const int32_t* lenX, const int32_t* lenY, int64_t Bx, int64_t By,
+                      int64_t Tx, int64_t Ty, const float* tau, const float* gX, int64_t gx0, int64_t gx1,
+                      const float* gY, int64_t gy0, int64_t gy1, const int16_t* argX, const int16_t* argY, float2* w2,
+                      uint32_t* inv, uint32_t* grp2, float* dX, cudaStream_t st);
+
 struct FilipWs {
-  __nv_bfloat16 *Ar, *Br, *AT, *BT;
-  float *pa, *pb;
+  __nv_bfloat16 *Ar, *Br;
+  float *pa, *pb;        // forward: per-warp partial sums of the masked means
+  float2* w2;            // backward (one side at a time): pair weights,
+  uint32_t* inv;         //   scatter entries sorted by target row,
+  uint32_t* grp2;        //   (first entry | count << 16) per group of target rows
   size_t total;
   bool ok;
 };
@@ -479,10 +260,11 @@ static FilipWs filip_carve(void* ws, size_t ws_bytes, int64_t Ba, int64_t Bb, in
   FilipWs f;
   f.Ar = w.take<__nv_bfloat16>((size_t)Ba * TA * fl::kDim);
   f.Br = w.take<__nv_bfloat16>((size_t)Bb * TB * fl::kDim);
-  f.AT = w.take<__nv_bfloat16>((size_t)Ba * fl::kDim * tld(TA));
-  f.BT = w.take<__nv_bfloat16>((size_t)Bb * fl::kDim * tld(TB));
   f.pa = w.take<float>((size_t)Ba * Bb * np_of(TA));
   f.pb = w.take<float>((size_t)Ba * Bb * np_of(TB));
+  f.inv = w.take<uint32_t>(filip_gather_inv_elems(Ba, Bb, TA, TB));
+  f.grp2 = w.take<uint32_t>(filip_gather_grp_elems(Ba, Bb, TA, TB));
+  f.w2 = w.take<float2>((size_t)Ba * Bb);
   f.total = align_up(w.off, 1024);
   f.ok = ws != nullptr && w.ok();
   return f;
@@ -492,10 +274,9 @@ size_t tc_filip_workspace(int64_t Ba, int64_t Bb, int64_t TA, int64_t TB) {
   return filip_carve(nullptr, 0, Ba, Bb, TA, TB).total + 1024;
 }
 
-static int filip_prep(const float* h, const int32_t* len, int64_t B, int64_t T, __nv_bfloat16* rows, __nv_bfloat16* colsT,
-                      cudaStream_t st) {
-  dim3 grid((unsigned)ceil_div(tld(T), 32), (unsigned)B);
-  filip_prep_kernel<<<grid, 256, 0, st>>>(h, len, (int)T, tld(T), rows, colsT);
+static int filip_prep(const float* h, const int32_t* len, int64_t B, int64_t T, __nv_bfloat16* rows, cudaStream_t st) {
+  const int64_t blocks = std::min<int64_t>(ceil_div(B * T, 8), (int64_t)device_sm_count() * 16);
+  filip_prep_kernel<<<(unsigned)blocks, 256, 0, st>>>(h, len, B, (int)T, rows);
   PCLIP_CHECK_LAUNCH();
   return PCLIP_OK;
 }
@@ -508,7 +289,7 @@ static int tc_side_fwd(const __nv_bfloat16* X, const __nv_bfloat16* Y, const int
   PCLIP_TRY(make_tmap_bf16_3d(&my, Y, (uint64_t)By, (uint64_t)Ty, fl::kDim, fl::kTile, 64));
   const int np = np_of(Tx);
   const int64_t ctas = ceil_div(Tx, fl::kRows) * Bx;
-  int ysplit = (int)std::max<int64_t>(1, std::min<int64_t>(By, ceil_div(148, ctas)));
+  int ysplit = (int)std::max<int64_t>(1, std::min<int64_t>(By, ceil_div(device_sm_count(), ctas)));
   const int yps = (int)ceil_div(By, ysplit);
   ysplit = (int)ceil_div(By, yps);
   FilipFwdArgs a{(int)Bx, (int)By, (int)Tx, (int)Ty, lenX, lenY, yps, part, np, arg};
@@ -528,40 +309,29 @@ int tc_filip_fwd(const float* hA, const float* hB, const int32_t* lenA, const in
                 PCLIP_ERR_INVALID, "filip: hA / hB must be 16-byte aligned");
   FilipWs f = filip_carve(ws, ws_bytes, Ba, Bb, TA, TB);
   PCLIP_REQUIRE(f.ok, PCLIP_ERR_WORKSPACE, "filip_fwd: workspace too small");
-  PCLIP_TRY(filip_prep(hA, lenA, Ba, TA, f.Ar, f.AT, st));
-  PCLIP_TRY(filip_prep(hB, lenB, Bb, TB, f.Br, f.BT, st));
+  PCLIP_TRY(filip_prep(hA, lenA, Ba, TA, f.Ar, st));
+  PCLIP_TRY(filip_prep(hB, lenB, Bb, TB, f.Br, st));
   PCLIP_TRY(tc_side_fwd(f.Ar, f.Br, lenA, lenB, Ba, Bb, TA, TB, tau, f.pa, argA, simA, Bb, 1, st));
   PCLIP_TRY(tc_side_fwd(f.Br, f.Ar, lenB, lenA, Bb, Ba, TB, TA, tau, f.pb, argB, simB, 1, Bb, st));
   return PCLIP_OK;
 }
 
-static int tc_side_bwd(const __nv_bfloat16* YT, const int32_t* lenX, const int32_t* lenY, int64_t Bx, int64_t By,
-                       int64_t Tx, int64_t Ty, const float* tau, const float* gX, int64_t gx0, int64_t gx1,
-                       const float* gY, int64_t gy0, int64_t gy1, const int16_t* argX, const int16_t* argY, float* dX,
-                       cudaStream_t st) {
-  CUtensorMap my;
-  PCLIP_TRY(make_tmap_bf16_3d(&my, YT, (uint64_t)By, fl::kDim, (uint64_t)tld(Ty), fl::kTile, 64));
-  FilipBwdArgs a{(int)Bx, (int)By, (int)Tx, (int)Ty, lenX, lenY, tau, gX, gx0, gx1, gY, gy0, gy1, argX, argY, dX};
-  PCLIP_CHECK_CUDA(
-      cudaFuncSetAttribute(tc_filip_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fl::kBwdSmem));
-  dim3 grid((unsigned)ceil_div(Tx, fl::kRows), (unsigned)Bx);
-  tc_filip_grad_kernel<<<grid, fl::kThreads, fl::kBwdSmem, st>>>(my, a);
-  PCLIP_CHECK_LAUNCH();
-  return PCLIP_OK;
-}
-
-
 int tc_filip_bwd(const float* hA, const float* hB, const int32_t* lenA, const int32_t* lenB, int64_t Ba, int64_t Bb,
                  int64_t TA, int64_t TB, int D, const float* tau, const int16_t* argA, const int16_t* argB,
                  const float* gA, const float* gB, float* dhA, float* dhB, void* ws, size_t ws_bytes, cudaStream_t st) {
   PCLIP_REQUIRE(D == fl::kDim, PCLIP_ERR_UNSUPPORTED, "filip: bf16 tensor-core path needs D == %d (got %d)", fl::kDim, D);
+  PCLIP_REQUIRE((reinterpret_cast<uintptr_t>(hA) & 15) == 0 && (reinterpret_cast<uintptr_t>(hB) & 15) == 0,
+                PCLIP_ERR_INVALID, "filip: hA / hB must be 16-byte aligned");
   FilipWs f = filip_carve(ws, ws_bytes, Ba, Bb, TA, TB);
   PCLIP_REQUIRE(f.ok, PCLIP_ERR_WORKSPACE, "filip_bwd: workspace too small");
-  // the operand copies are rebuilt (HBM-bound, ~1% of the step) so that fwd and bwd may use different workspaces
-  PCLIP_TRY(filip_prep(hA, lenA, Ba, TA, f.Ar, f.AT, st));
-  PCLIP_TRY(filip_prep(hB, lenB, Bb, TB, f.Br, f.BT, st));
-  PCLIP_TRY(tc_side_bwd(f.BT, lenA, lenB, Ba, Bb, TA, TB, tau, gA, Bb, 1, gB, 1, Bb, argA, argB, dhA, st));
-  PCLIP_TRY(tc_side_bwd(f.AT, lenB, lenA, Bb, Ba, TB, TA, tau, gB, 1, Bb, gA, Bb, 1, argB, argA, dhB, st));
+  // the bf16 token rows are rebuilt (HBM-bound, ~1% of the step) so that fwd and bwd may use different workspaces
+  PCLIP_TRY(filip_prep(hA, lenA, Ba, TA, f.Ar, st));
+  PCLIP_TRY(filip_prep(hB, lenB, Bb, TB, f.Br, st));
+  // dhA: gather through argA, scatter through the inverse of argB; then the mirror image for dhB
+  PCLIP_TRY(filip_gather_side(f.Br, lenA, lenB, Ba, Bb, TA, TB, tau, gA, Bb, 1, gB, 1, Bb, argA, argB, f.w2, f.inv, f.grp2,
+                              dhA, st));
+  PCLIP_TRY(filip_gather_side(f.Ar, lenB, lenA, Bb, Ba, TB, TA, tau, gB, 1, Bb, gA, Bb, 1, argB, argA, f.w2, f.inv, f.grp2,
+                              dhB, st));
   return PCLIP_OK;
 }
 
