@@ -2,7 +2,7 @@
 NVCC      ?= /usr/local/cuda/bin/nvcc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVCCFLAGS := -O3 -std=c++17 -lineinfo $(ARCH) -Xcompiler -fPIC,-Wall,-Wno-unused-function --expt-relaxed-constexpr \
-             -Xptxas -v
+             -Xptxas -v $(EXTRA)
 CSRC      := protein-clip_b200/csrc
 SRCS      := $(wildcard $(CSRC)/*.cu)
 OBJS      := $(patsubst $(CSRC)/%.cu,build/%.o,$(SRCS))

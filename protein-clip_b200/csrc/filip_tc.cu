@@ -81,6 +81,47 @@ constexpr int kFwdStages = 4;
 constexpr uint32_t kFwdSmem = kTileBytes * (kH + kFwdStages) + 256 + 1024;
 }  // namespace fl
 
+namespace fl {
+constexpr uint32_t kNegKey = 0xff7fffe0u;   // key of -FLT_MAX
+
+template <int E>
+__device__ __forceinline__ void make_keys(const uint32_t (&r)[32], const uint32_t keep, float (&k)[32]) {
+  if constexpr (E < 32) {
+    uint32_t key;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(key) : "r"(r[E]), "r"(keep), "n"(31 - E));   // (r & keep) | (31 - E)
+    k[E] = __uint_as_float(key);
+    make_keys<E + 1>(r, keep, k);
+  }
+}
+
+__device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }   // one FMNMX3
+
+// Maximum and arg-maximum of 32 scores of one token row in 1.5 instructions per score: every score becomes a KEY (its
+// 5 low mantissa bits replaced by 31 - column, one LOP3), the keys go through a 3-input max tree (16 FMNMX3), and
+// the winner is compared with the running key on the score bits only, so that among scores equal to 2^-18 relative
+// the lowest column of the chunk wins and an earlier chunk beats a later one (non-negative maxima; the reference's
+// amax backward splits exact ties).  The round-1 epilogue (compare, select, select per score, one
+// 64-deep dependent chain per chunk) paced the kernel at 1160 clk per tile pair against 1024 clk of MMA: 8.0 ms per
+// forward at cfg 3, 6.8 ms with this one.  Making half of the keys on the FMA pipe (IMAD.HI + IMAD) was slower (7.5 ms).
+__device__ __forceinline__ void chunk_max(const uint32_t (&r)[32], const int col0, uint32_t& mk, int& base) {
+  float k[32];
+  uint32_t keep;   // 0xffffffe0 in a register the optimiser cannot see through: (r & keep) | imm is then ONE LOP3
+  asm("mov.u32 %0, 0xffffffe0;" : "=r"(keep));
+  make_keys<0>(r, keep, k);
+  float a[11];
+#pragma unroll
+  for (int j = 0; j < 10; ++j) a[j] = max3(k[3 * j], k[3 * j + 1], k[3 * j + 2]);
+  a[10] = fmaxf(k[30], k[31]);
+  const float b0 = max3(a[0], a[1], a[2]), b1 = max3(a[3], a[4], a[5]), b2 = max3(a[6], a[7], a[8]);
+  const float b3 = fmaxf(a[9], a[10]);
+  const uint32_t m = __float_as_uint(fmaxf(max3(b0, b1, b2), b3));
+  if (__uint_as_float(m | 31u) > __uint_as_float(mk | 31u)) {
+    mk = m;
+    base = col0;
+  }
+}
+}  // namespace fl
+
 __global__ void __launch_bounds__(fl::kThreads, 1)
 tc_filip_max_kernel(const __grid_constant__ CUtensorMap tx, const __grid_constant__ CUtensorMap ty,
                     const FilipFwdArgs args) {
@@ -181,8 +222,8 @@ tc_filip_max_kernel(const __grid_constant__ CUtensorMap tx, const __grid_constan
     int it = 0;
     for (int by = y0; by < y1; ++by) {
       const int ly = min(args.lenY[by], args.Ty);
-      float m = -FLT_MAX;
-      int am = 0;
+      uint32_t mk = kNegKey;   // running maximum as a key: score with its 5 low mantissa bits replaced by 31 - column
+      int base = 0;            // first column of the 32-column chunk the running maximum came from
       if (live) {
         for (int s0 = 0; s0 < ly; s0 += kTile, ++it) {
           const int buf = it & 1;
@@ -191,30 +232,44 @@ tc_filip_max_kernel(const __grid_constant__ CUtensorMap tx, const __grid_constan
           tc_fence_after_sync();
           const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 2 + buf) * kTile;
           const int nvalid = ly - s0;  // >= 1; columns >= nvalid of this tile are pads
-#pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            if (c * 32 >= nvalid) break;  // warp-uniform
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(taddr + c * 32, r);
+          uint32_t ra[32], rb[32];
+          if (nvalid >= kTile) {
+            // full tile: the next chunk's TMEM load is in flight while the current one is reduced, and the accumulator
+            // goes back to the MMA warp as soon as the last load has landed
+            tmem_ld_32x32b_x32(taddr, ra);
             tmem_ld_wait();
-            if (nvalid - c * 32 < 32) {
+            tmem_ld_32x32b_x32(taddr + 32, rb);
+            chunk_max(ra, s0, mk, base);
+            tmem_ld_wait();
+            tmem_ld_32x32b_x32(taddr + 64, ra);
+            chunk_max(rb, s0 + 32, mk, base);
+            tmem_ld_wait();
+            tmem_ld_32x32b_x32(taddr + 96, rb);
+            chunk_max(ra, s0 + 64, mk, base);
+            tmem_ld_wait();
+            tc_fence_before_sync();
+            mbar_arrive(&t_empty[h * 2 + buf]);
+            chunk_max(rb, s0 + 96, mk, base);
+          } else {
+#pragma unroll 1
+            for (int c = 0; c * 32 < nvalid; ++c) {   // warp-uniform
+              tmem_ld_32x32b_x32(taddr + c * 32, ra);
+              tmem_ld_wait();
+              if (nvalid - c * 32 < 32) {
 #pragma unroll
-              for (int e = 0; e < 32; ++e)
-                if (c * 32 + e >= nvalid) r[e] = __float_as_uint(-FLT_MAX);
-            }
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const float v = __uint_as_float(r[e]);
-              if (v > m) {  // strict: the first maximiser wins (torch.max / the oracle's convention)
-                m = v;
-                am = s0 + c * 32 + e;
+                for (int e = 0; e < 32; ++e)
+                  if (c * 32 + e >= nvalid) ra[e] = __float_as_uint(-FLT_MAX);
               }
+              chunk_max(ra, s0 + c * 32, mk, base);
             }
+            tc_fence_before_sync();
+            mbar_arrive(&t_empty[h * 2 + buf]);
           }
-          tc_fence_before_sync();
-          mbar_arrive(&t_empty[h * 2 + buf]);
         }
       }
+      const int am = base + 31 - (int)(mk & 31u);
+      // the 5 bits the column index displaced are set to the middle of their range: |error| <= 2^-19 relative, unbiased
+      const float m = ly > 0 ? __uint_as_float((mk & ~31u) | 16u) : -FLT_MAX;
       const int64_t pair = (int64_t)bx * args.By + by;
       if (live && t < args.Tx) args.arg[pair * args.Tx + t] = (int16_t)am;
       float v = (live && t < lx) ? m : 0.f;
