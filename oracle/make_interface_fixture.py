@@ -23,6 +23,16 @@ def signatures(mod, names):
     return {n: str(inspect.signature(getattr(mod, n))) for n in names}
 
 
+def script_attrs():
+    import re
+    out = {}
+    for script in ("main.py", "main_2protein.py", "main_2protein_filip.py", "topk.py", "cosine_similarity.py"):
+        src = open(os.path.join(ref_loader.REFERENCE_ROOT, script)).read()
+        for mod, attr in re.findall(r"\b(models|training_utils|training_utils_filip|visualizations|seed)\.(\w+)", src):
+            out.setdefault(mod, set()).add(attr)
+    return {m: sorted(v) for m, v in sorted(out.items())}
+
+
 def main():
     ref = ref_loader.load()
     esm = tiny_esm()
@@ -42,7 +52,14 @@ def main():
             "ExtendedFILIP._filip_similarity_score": str(inspect.signature(M.ExtendedFILIP._filip_similarity_score)),
         },
         "visualizations": signatures(ref.visualizations, ["_compute_embedding_cosine_similarities",
-                                                          "_compute_embedding_cosine_similarities_filip"]),
+                                                          "_compute_embedding_cosine_similarities_filip",
+                                                          "plot_embedding_cosine_similarities",
+                                                          "plot_embedding_cosine_similarities_filip",
+                                                          "plot_loss_curves", "plot_clustering",
+                                                          "plot_protein_lengths", "_save_plot"]),
+        # every attribute the entry scripts touch on the modules this repo replaces (the scripts must not
+        # meet an AttributeError at start-up)
+        "script_attrs": script_attrs(),
         "state_dict_keys": {
             "ExtendedCLIP": sorted(k for k in M.ExtendedCLIP(40, 128, 2, 2, 0.1, esm).state_dict()
                                    if "esm_model" not in k),

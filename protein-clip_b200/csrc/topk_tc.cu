@@ -355,9 +355,10 @@ topk_rescore_kernel(const float* __restrict__ q, const float* __restrict__ bank,
     if (bc >= 0) kth = bs; else have_k = false;
   }
   if (lane == 0 && tdisc > -FLT_MAX) {
-    // |bf16-path score - fp32-chain score| <= (2^-8 (1 + 2^-9) + D 2^-23) ||q|| ||b||  (bf16 RN of both operands,
-    // fp32 accumulation on both sides); 1.02 covers the second-order terms.
-    const float eps = (0.00390625f * 1.02f + 128.0f * 1.1920929e-7f) * qnorm[row] * __int_as_float(*bmax_bits);
+    // bf16 has an 8-bit significand: round-to-nearest moves each operand by at most 2^-8 relative, so
+    // |bf16-path score - fp32-chain score| <= (2^-7 (1 + 2^-9) + D 2^-23) ||q|| ||b||  (Cauchy-Schwarz over the D
+    // products; fp32 accumulation on both sides); the factor 1.01 covers the second-order term with room to spare.
+    const float eps = (0.0078125f * 1.01f + 128.0f * 1.1920929e-7f) * qnorm[row] * __int_as_float(*bmax_bits);
     if (!have_k || !(kth > tdisc + eps)) unsafe_list[atomicAdd(unsafe_count, 1)] = (int32_t)row;
   }
 }

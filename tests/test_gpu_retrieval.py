@@ -119,6 +119,37 @@ def test_topk_unprovable_rows_are_recomputed_exactly(ops, Q):
     check_topk(i32.cpu(), s32.cpu(), q, bank, 10)
 
 
+def test_topk_adversarial_bf16_midpoints(ops):
+    """every entry of the query and of one bank row sits just above a bf16 rounding midpoint (1 + 2^-8 rounds
+    to 1), all signs aligned, so the bf16 score of that row falls 2^-7 (relative) below its fp32 score -- the worst
+    case of the exactness bound.  30 decoy rows are exact in bf16 and score higher than the victim in bf16 but lower in
+    fp32: the victim is pushed out of the 24-entry candidate list although it is the true top-1.  With the round-1
+    bound (2^-8: half the rigorous one) the query passed the margin test and the wrong answer was returned; with the
+    rigorous bound the margin test fails and the exact kernel recomputes the row."""
+    a = 0.0625
+    up = 1.0 + 2.0 ** -8
+    g = torch.Generator().manual_seed(11)
+    N, Q, k = 4096, 8, 10
+    bank = 0.01 * torch.randn(N, 128, generator=g)
+    victim = 3000
+    bank[victim] = a * up
+    for i in range(30):                       # decoy i: bf16-exact, 8 entries one bf16 ulp up
+        row = torch.full((128,), a)
+        row[4 * i: 4 * i + 8] = a * (1.0 + 2.0 ** -7)
+        bank[100 + 7 * i] = row
+    q = torch.randn(Q, 128, generator=g)
+    q[:4] = a * up
+    assert float((q[0].double() @ bank[victim].double())) > float((q[0].double() @ bank[100].double()))
+    assert float(q[0].bfloat16().double() @ bank[victim].bfloat16().double()) < \
+        float(q[0].bfloat16().double() @ bank[100].bfloat16().double())
+    i32, s32, _ = ops.topk(q.cuda(), bank.cuda(), k, compute=ops.F32)
+    i16, s16, unsafe = ops.topk(q.cuda(), bank.cuda(), k, compute=ops.BF16)
+    assert i32[:4, 0].tolist() == [victim] * 4
+    assert torch.equal(i16, i32) and torch.equal(s16, s32)
+    assert int(unsafe) >= 4
+    check_topk(i16.cpu(), s16.cpu(), q, bank, k)
+
+
 def test_topk_bank_sharded_merge(ops):
     from pclip import synth
     bank, q, pos = synth.retrieval_bank(9000, 150, cfg_id=72, dup_every=5)

@@ -85,6 +85,34 @@ def test_module_signatures_match_reference(iface):
         assert callable(getattr(training_utils, fn))
 
 
+def test_every_attribute_the_scripts_use_exists(iface):
+    """main*.py / topk.py / cosine_similarity.py must not meet an AttributeError on the modules this repo replaces."""
+    import importlib
+    for mod, attrs in iface["script_attrs"].items():
+        m = importlib.import_module(f"modules.{mod}")
+        for a in attrs:
+            assert hasattr(m, a), f"modules.{mod}.{a} is used by the reference's scripts but missing here"
+
+
+def test_cpu_plot_helpers(tmp_path):
+    """The plotting helpers the scripts call at start-up and after the last epoch (CPU only; reference naming
+    'figures/figure N.png' with one shared counter, ref: modules/visualizations.py:191-210)."""
+    from modules import visualizations as vis
+    (tmp_path / "protein1.fasta").write_text(">a\nACDE\nFG\n>b\nAAA\n")
+    (tmp_path / "protein2.fasta").write_text(">c\nACDEFGHIK\n")
+    (tmp_path / "protein2DB_clustered.tsv").write_text("c1\tc1\nc1\tx\nc2\tc2\n")
+    assert vis._fasta_lengths(tmp_path / "protein1.fasta") == [6, 3]
+    first = vis._save_plot(str(tmp_path))
+    n0 = int(os.path.basename(first)[len("figure "):-4])
+    vis.plot_protein_lengths(str(tmp_path), tmp_path)
+    vis.plot_clustering(str(tmp_path), str(tmp_path), prefix="protein2")
+    vis.plot_loss_curves(str(tmp_path), [3.0, 2.5], [3.1, 2.9], 256, 16)
+    nxt = vis._save_plot(str(tmp_path))
+    assert nxt.endswith(f"figure {n0 + 4}.png") and os.path.dirname(nxt) == str(tmp_path / "figures")
+    made = sorted(os.listdir(tmp_path / "figures"))
+    assert len(made) >= 3 and all(f.startswith("figure ") for f in made)
+
+
 def test_state_dict_keys_match_reference(iface):
     from modules import models
 
