@@ -173,9 +173,11 @@ enum pclip_score_op { PCLIP_SCORE_DOT = 0, PCLIP_SCORE_EXP = 1 };
 int pclip_scores(const float* q, const float* bank, int64_t Q, int64_t N, int32_t D, int32_t op,
                  const float* neg_tau /* dev [1] or NULL */, float* out, pclip_stream_t stream);
 
-/* rank[q] = 1 + #{ n : q.bank_n > q.bank_pos[q] }  in fp32 (every score computed by the same FFMA chain) */
+/* rank[q] = 1 + #{ n : q.bank_n > q.bank_pos[q] }  in fp32 (every score computed by the same FFMA chain).
+ * One call ranks ALL Q queries against the bank (topk.py:47-51 loops 256 single-query calls). */
+size_t pclip_rank_workspace_bytes(int64_t Q);
 int pclip_rank_of_positive(const float* q, const float* bank, const int64_t* pos, int64_t Q, int64_t N, int32_t D,
-                           int32_t* rank, pclip_stream_t stream);
+                           int32_t* rank, void* workspace, size_t workspace_bytes, pclip_stream_t stream);
 
 size_t pclip_topk_workspace_bytes(int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute);
 /* top-k by dot product, descending, ties -> lower index.  idx [Q,k] int64 (+ index_base), score [Q,k] fp32.
@@ -186,6 +188,17 @@ size_t pclip_topk_workspace_bytes(int64_t Q, int64_t N, int32_t D, int32_t k, in
 int pclip_topk(const float* q, const float* bank, int64_t Q, int64_t N, int32_t D, int32_t k, int32_t compute,
                int64_t index_base, int64_t* idx, float* score, int32_t* n_unsafe, void* workspace,
                size_t workspace_bytes, pclip_stream_t stream);
+/* Persistent bf16 image of a bank for repeated bf16 top-k calls (an embedding bank is built once and queried many
+ * times): pclip_topk converts the fp32 bank on every call (3 N D bytes of HBM traffic), which
+ * dominates when a call carries few queries.  `prepared` is caller memory of pclip_topk_bank_bytes(N, D) bytes,
+ * 1024-byte aligned; `bank` (fp32) is still needed by pclip_topk_prepared for the exact re-scoring. */
+size_t pclip_topk_bank_bytes(int64_t N, int32_t D);
+int pclip_topk_prepare_bank(const float* bank, int64_t N, int32_t D, void* prepared, size_t prepared_bytes,
+                            pclip_stream_t stream);
+int pclip_topk_prepared(const float* q, const float* bank, const void* prepared, int64_t Q, int64_t N, int32_t D,
+                        int32_t k, int64_t index_base, int64_t* idx, float* score, int32_t* n_unsafe, void* workspace,
+                        size_t workspace_bytes, pclip_stream_t stream);
+
 /* merge per-shard (idx, score) candidate lists [n_lists, Q, k] into the global top-k (bank-sharded mode) */
 int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, int32_t n_lists, int32_t k,
                      int64_t* idx, float* score, pclip_stream_t stream);

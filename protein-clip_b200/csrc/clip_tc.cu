@@ -23,7 +23,7 @@ constexpr uint32_t kPanelBytes = 128 * 128;   // [128 rows x 64 bf16]
 constexpr uint32_t kTileBytes = 2 * kPanelBytes;
 constexpr int kThreads = 192;
 constexpr int kEpiThreads = 128;
-constexpr int kPlanSms = 148;
+static int plan_sms() { return std::max(1, device_sm_count()); }
 constexpr float kLog2e = 1.4426950408889634f;
 
 // ---- UMMA descriptors for a K-major SW128 panel pair ------------------------------------------------------------
@@ -209,7 +209,7 @@ __global__ void sum_partials_kernel(const float* __restrict__ partial, int nspli
 
 static void plan_split(int64_t Ma, int64_t Nb, int n_sides, int max_split, int* nsplit, int* tps) {
   const int64_t rb = ceil_div(Ma, kTile), nt = ceil_div(Nb, kTile);
-  int64_t want = ceil_div(4 * kPlanSms, rb * n_sides);
+  int64_t want = ceil_div(4 * plan_sms(), rb * n_sides);
   if (want > nt) want = nt;
   if (want > max_split) want = max_split;
   if (want < 1 || nt <= 2) want = 1;  // tiny problems: one launch, no partial-sum pass

@@ -104,7 +104,10 @@ int clip_generation();
 // BF16 tcgen05 candidate selection + fp32 re-scoring (topk_tc.cu)
 size_t tc_topk_workspace(int64_t Q, int64_t N, int k);
 int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
-            float* score, int32_t* n_unsafe, void* ws, size_t ws_bytes, cudaStream_t st);
+            float* score, int32_t* n_unsafe, void* ws, size_t ws_bytes, cudaStream_t st,
+            const void* prepared = nullptr);
+size_t tc_topk_bank_bytes(int64_t N);
+int tc_topk_prepare_bank(const float* bank, int64_t N, int D, void* prepared, size_t prepared_bytes, cudaStream_t st);
 // FILIP (filip.cu: fp32 path + tails; filip_tc.cu: bf16 tcgen05 path)
 int filip_finalize(const float* part, int np, const int32_t* lenX, int Bx, int By, int Tx, const float* tau, float* out,
                    int64_t so0, int64_t so1, cudaStream_t st);

@@ -383,7 +383,7 @@ int pclip_scale_by_scalar(const float* in, const float* g, int64_t n, float* out
   PCLIP_TRY(require_device());
   PCLIP_REQUIRE(in && g && out && n >= 0, PCLIP_ERR_INVALID, "scale_by_scalar: bad argument");
   if (n == 0) return PCLIP_OK;
-  const int blocks = (int)std::min<int64_t>(ceil_div(n, 256), 148 * 16);
+  const int blocks = (int)std::min<int64_t>(ceil_div(n, 256), (int64_t)device_sm_count() * 16);
   scale_by_scalar_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(in, g, n, out);
   PCLIP_CHECK_LAUNCH();
   return PCLIP_OK;

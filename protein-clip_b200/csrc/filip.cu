@@ -158,7 +158,7 @@ static int simt_filip_side_fwd(const float* X, const float* Y, const int32_t* le
                                int Tx, int Ty, int D, const float* tau, float* part, int16_t* arg, float* out,
                                int64_t so0, int64_t so1, cudaStream_t st) {
   const int np = (int)ceil_div(Tx, kBM);
-  int ysplit = (int)std::max<int64_t>(1, std::min<int64_t>(By, ceil_div(2 * 148, (int64_t)np * Bx)));
+  int ysplit = (int)std::max<int64_t>(1, std::min<int64_t>(By, ceil_div(2 * device_sm_count(), (int64_t)np * Bx)));
   const int yps = (int)ceil_div(By, ysplit);
   ysplit = (int)ceil_div(By, yps);
   dim3 grid((unsigned)np, (unsigned)Bx, (unsigned)ysplit);

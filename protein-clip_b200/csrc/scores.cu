@@ -229,7 +229,7 @@ __global__ void topk_merge_kernel(const int64_t* __restrict__ idx_in, const floa
 
 static void plan_n_split(int64_t Q, int64_t N, int max_lists, int* nsplit, int* tps) {
   const int64_t rb = ceil_div(Q, kBM), nt = ceil_div(N, kBN);
-  int64_t want = ceil_div(2 * 148, rb);
+  int64_t want = ceil_div(2 * device_sm_count(), rb);
   if (want > nt) want = nt;
   if (want > max_lists) want = max_lists;
   if (want < 1) want = 1;
@@ -296,14 +296,17 @@ int pclip_scores(const float* q, const float* bank, int64_t Q, int64_t N, int32_
   return PCLIP_OK;
 }
 
+size_t pclip_rank_workspace_bytes(int64_t Q) { return align_up((size_t)Q * sizeof(float), 1024); }
+
 int pclip_rank_of_positive(const float* q, const float* bank, const int64_t* pos, int64_t Q, int64_t N, int32_t D,
-                           int32_t* rank, pclip_stream_t stream) {
+                           int32_t* rank, void* workspace, size_t workspace_bytes, pclip_stream_t stream) {
   PCLIP_TRY(require_device());
   PCLIP_REQUIRE(q && bank && pos && rank && Q > 0 && N > 0 && D > 0, PCLIP_ERR_INVALID, "rank: bad argument");
+  PCLIP_REQUIRE(workspace && (reinterpret_cast<uintptr_t>(workspace) & 1023) == 0 &&
+                    workspace_bytes >= pclip_rank_workspace_bytes(Q),
+                PCLIP_ERR_WORKSPACE, "rank: workspace missing, misaligned or too small");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // the positive's score is parked in the rank buffer's tail?  no: keep it simple, one small scratch via cudaMallocAsync
-  float* pos_score = nullptr;
-  PCLIP_CHECK_CUDA(cudaMallocAsync(&pos_score, (size_t)Q * sizeof(float), st));
+  float* pos_score = static_cast<float*>(workspace);   // the positives' scores, [Q]
   pos_score_kernel<<<(unsigned)ceil_div(Q, 128), 128, 0, st>>>(q, bank, pos, Q, D, pos_score, rank);
   PCLIP_CHECK_LAUNCH();
   int nsplit, tps;
@@ -311,7 +314,6 @@ int pclip_rank_of_positive(const float* q, const float* bank, const int64_t* pos
   dim3 grid((unsigned)ceil_div(Q, kBM), (unsigned)nsplit);
   rank_kernel<<<grid, 256, 0, st>>>(q, bank, pos_score, Q, N, D, tps, rank);
   PCLIP_CHECK_LAUNCH();
-  PCLIP_CHECK_CUDA(cudaFreeAsync(pos_score, st));
   return PCLIP_OK;
 }
 
@@ -333,6 +335,29 @@ int pclip_topk(const float* q, const float* bank, int64_t Q, int64_t N, int32_t 
   PCLIP_REQUIRE(compute == PCLIP_COMPUTE_F32, PCLIP_ERR_UNSUPPORTED, "topk: unknown compute mode %d", compute);
   if (n_unsafe) PCLIP_CHECK_CUDA(cudaMemsetAsync(n_unsafe, 0, sizeof(int32_t), st));
   return simt_topk(q, bank, Q, N, D, k, index_base, idx, score, workspace, workspace_bytes, st);
+}
+
+size_t pclip_topk_bank_bytes(int64_t N, int32_t D) {
+  (void)D;
+  return tc_topk_bank_bytes(N);
+}
+
+int pclip_topk_prepare_bank(const float* bank, int64_t N, int32_t D, void* prepared, size_t prepared_bytes,
+                            pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(bank && N > 0, PCLIP_ERR_INVALID, "topk_prepare_bank: bad argument");
+  return tc_topk_prepare_bank(bank, N, D, prepared, prepared_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int pclip_topk_prepared(const float* q, const float* bank, const void* prepared, int64_t Q, int64_t N, int32_t D,
+                        int32_t k, int64_t index_base, int64_t* idx, float* score, int32_t* n_unsafe, void* workspace,
+                        size_t workspace_bytes, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(q && bank && prepared && idx && score && Q > 0 && N > 0 && D > 0, PCLIP_ERR_INVALID,
+                "topk_prepared: bad argument");
+  PCLIP_REQUIRE(k >= 1 && k <= kMaxK, PCLIP_ERR_UNSUPPORTED, "topk: k must be in [1, %d]", kMaxK);
+  return tc_topk(q, bank, Q, N, D, k, index_base, idx, score, n_unsafe, workspace, workspace_bytes,
+                 static_cast<cudaStream_t>(stream), prepared);
 }
 
 int pclip_topk_merge(const int64_t* idx_in, const float* score_in, int64_t Q, int32_t n_lists, int32_t k,

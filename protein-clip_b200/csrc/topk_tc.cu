@@ -374,7 +374,7 @@ static int cand_per_query(int k) { return k <= 6 ? 16 : (k <= 10 ? 24 : tk::kMax
 // tile.  512 query blocks (131 072 queries): 2 splits = 6.9 waves of 16 384 tiles instead of 3.5 -> 4 waves of 32 768.
 static void plan_topk_split(int64_t Q, int64_t N, int kc, int* nsplit, int* tps) {
   const int64_t rb = ceil_div(Q, tk::kRows), nt = ceil_div(N, tk::kTile);
-  const int64_t sms = 148, overhead = 128;
+  const int64_t sms = std::max(1, device_sm_count()), overhead = 128;
   const int64_t max_ns = std::max<int64_t>(1, std::min<int64_t>(kMaxCandTotal / kc, nt));
   int64_t best_ns = 1, best_cost = -1;
   for (int64_t ns = 1; ns <= max_ns; ++ns) {
@@ -433,8 +433,27 @@ size_t tc_topk_workspace(int64_t Q, int64_t N, int k) {
   return align_up(w.off, 1024) + 1024;
 }
 
+// Prepared bank image: bf16 rows [(N + kTile) x 128] followed (1024-byte aligned) by the bits of the largest row norm.
+size_t tc_topk_bank_bytes(int64_t N) {
+  return align_up((size_t)(N + tk::kTile) * tk::kDim * sizeof(__nv_bfloat16), 1024) + 1024;
+}
+
+int tc_topk_prepare_bank(const float* bank, int64_t N, int D, void* prepared, size_t prepared_bytes, cudaStream_t st) {
+  PCLIP_REQUIRE(D == tk::kDim, PCLIP_ERR_UNSUPPORTED, "topk: bf16 tensor-core path needs D == %d (got %d)", tk::kDim, D);
+  PCLIP_REQUIRE(prepared && (reinterpret_cast<uintptr_t>(prepared) & 1023) == 0 && prepared_bytes >= tc_topk_bank_bytes(N),
+                PCLIP_ERR_WORKSPACE, "topk_prepare_bank: buffer missing, misaligned or smaller than %zu bytes",
+                tc_topk_bank_bytes(N));
+  PCLIP_REQUIRE((reinterpret_cast<uintptr_t>(bank) & 15) == 0, PCLIP_ERR_INVALID, "topk: bank must be 16-byte aligned");
+  int32_t* maxbits = reinterpret_cast<int32_t*>(static_cast<char*>(prepared) + tc_topk_bank_bytes(N) - 1024);
+  PCLIP_CHECK_CUDA(cudaMemsetAsync(maxbits, 0, sizeof(int32_t), st));
+  to_bf16_norm_kernel<<<device_sm_count() * 8, 256, 0, st>>>(bank, N, static_cast<__nv_bfloat16*>(prepared), nullptr,
+                                                             maxbits);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
 int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,
-            float* score, int32_t* n_unsafe, void* ws, size_t ws_bytes, cudaStream_t st) {
+            float* score, int32_t* n_unsafe, void* ws, size_t ws_bytes, cudaStream_t st, const void* prepared) {
   PCLIP_REQUIRE(D == tk::kDim, PCLIP_ERR_UNSUPPORTED, "topk: bf16 tensor-core path needs D == %d (got %d)", tk::kDim, D);
   PCLIP_REQUIRE(N < (int64_t)0x7fffff00, PCLIP_ERR_UNSUPPORTED, "topk: N must fit 31 bits per call (shard the bank)");
   PCLIP_REQUIRE((reinterpret_cast<uintptr_t>(q) & 15) == 0 && (reinterpret_cast<uintptr_t>(bank) & 15) == 0,
@@ -449,14 +468,21 @@ int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int 
   PCLIP_REQUIRE(t.ok, PCLIP_ERR_WORKSPACE, "topk: workspace too small (%zu < %zu)", ws_bytes,
                 tc_topk_workspace(Q, N, k));
   PCLIP_CHECK_CUDA(cudaMemsetAsync(t.scalars, 0, 2 * sizeof(int32_t), st));
-  const int cblocks = 148 * 8;
+  const int cblocks = device_sm_count() * 8;
   to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(q, Q, t.qb, t.qnorm, nullptr);
   PCLIP_CHECK_LAUNCH();
-  to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(bank, N, t.bb, nullptr, t.scalars);
-  PCLIP_CHECK_LAUNCH();
+  const __nv_bfloat16* bb = t.bb;
+  if (prepared) {   // persistent bf16 bank (pclip_topk_prepare_bank): no 3 N D-byte conversion pass per call
+    bb = static_cast<const __nv_bfloat16*>(prepared);
+    PCLIP_CHECK_CUDA(cudaMemcpyAsync(t.scalars, static_cast<const char*>(prepared) + tc_topk_bank_bytes(N) - 1024,
+                                     sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  } else {
+    to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(bank, N, t.bb, nullptr, t.scalars);
+    PCLIP_CHECK_LAUNCH();
+  }
   CUtensorMap mq, mb;
   PCLIP_TRY(make_tmap_bf16_2d(&mq, t.qb, (uint64_t)Q, tk::kDim, tk::kDim, tk::kTile, 64));
-  PCLIP_TRY(make_tmap_bf16_2d(&mb, t.bb, (uint64_t)N, tk::kDim, tk::kDim, tk::kTile, 64));
+  PCLIP_TRY(make_tmap_bf16_2d(&mb, bb, (uint64_t)N, tk::kDim, tk::kDim, tk::kTile, 64));
   TopkArgs a{Q, N, kc, tps, t.cand_idx, t.cand_score};
   auto kern = kc == 16 ? tc_topk_kernel<16> : (kc == 24 ? tc_topk_kernel<24> : tc_topk_kernel<32>);
   PCLIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tk::kSmemBytes));

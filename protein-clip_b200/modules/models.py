@@ -111,7 +111,8 @@ class ExtendedFILIP(nn.Module):
         # h / ||h|| with NO eps, pads included (ref: :238-239): normalize_scale with tau=None, eps=0
         pep = ops.normalize_scale(pep, None, eps=0.0)
         rec = ops.normalize_scale(rec, None, eps=0.0)
-        return self._filip_similarity_score(pep, rec, pep_mask, rec_mask, self.temperature)
+        # tokenizer masks are right-padded (padding=True): lengths go straight to the kernel, no compaction pass
+        return ops.filip_similarity(pep, rec, pep_mask, rec_mask, self.temperature)
 
     @staticmethod
     def _masked_mean(t, mask, dim=1, eps=1e-6):
@@ -123,17 +124,29 @@ class ExtendedFILIP(nn.Module):
     @staticmethod
     def _mean_average_similarity_score(hA, hB, maskA, maskB, temperature):
         """Mean-pooled baseline similarity (unused by the scripts; ref: :266-290): plain means over T of the masked
-        tokens, then all-pairs dot products / temperature."""
+        tokens, then all-pairs dot products / temperature.  Differentiable like the reference's einsum (a [B, B] matmul
+        off the hot path: stock torch)."""
         pa = (hA * maskA[..., None]).mean(dim=1)
         pb = (hB * maskB[..., None]).mean(dim=1)
-        return ops.scores(pa, pb, "dot") / temperature if pa.is_cuda else pa @ pb.t() / temperature
+        return pa @ pb.t() / temperature
 
     @staticmethod
     def _filip_similarity_score(hA, hB, maskA, maskB, temperature, include_group=False):
         """Token-wise late interaction (ref: :292-356): S = <hA[a,t], hB[b,s]> / temperature on the valid tokens;
-        simA = masked mean over t of max_s, simB = masked mean over s of max_t.  Masks must be right-padded (what the
-        ESM tokenizer produces).  include_group=True returns the reference's [1, 1, bA, bB] layout."""
-        simA, simB = ops.filip_similarity(hA, hB, maskA, maskB, temperature)
+        simA = masked mean over t of max_s, simB = masked mean over s of max_t.
+
+        Any 0/1 mask is accepted, as in the reference: the valid tokens of every sample are moved to the front first
+        (max and mean do not depend on token order; the gather is differentiable), so the kernels only ever see
+        lengths.  include_group=True takes [m, b, t, d] / [n, b, t, d] inputs and returns [m, n, bA, bB] (:314-322): the
+        group pairs are evaluated one after the other."""
         if include_group:
-            return simA[None, None], simB[None, None]
-        return simA, simB
+            rows_a, rows_b = [], []
+            for m in range(hA.shape[0]):
+                pa, pb = zip(*(ExtendedFILIP._filip_similarity_score(hA[m], hB[n], maskA[m], maskB[n], temperature)
+                               for n in range(hB.shape[0])))
+                rows_a.append(torch.stack(pa))
+                rows_b.append(torch.stack(pb))
+            return torch.stack(rows_a), torch.stack(rows_b)
+        hA, lenA = ops.compact_tokens(hA, maskA)
+        hB, lenB = ops.compact_tokens(hB, maskB)
+        return ops.filip_similarity(hA, hB, lenA, lenB, temperature)

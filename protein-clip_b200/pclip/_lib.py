@@ -63,7 +63,11 @@ SIGNATURES = {
                                   _P, _P, _P, _SZ, _P]),
     "pclip_scale_by_scalar": (C.c_int, [_P, _P, _I64, _P, _P]),
     "pclip_scores": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _P, _P, _P]),
-    "pclip_rank_of_positive": (C.c_int, [_P, _P, _P, _I64, _I64, _I32, _P, _P]),
+    "pclip_rank_workspace_bytes": (_SZ, [_I64]),
+    "pclip_rank_of_positive": (C.c_int, [_P, _P, _P, _I64, _I64, _I32, _P, _P, _SZ, _P]),
+    "pclip_topk_bank_bytes": (_SZ, [_I64, _I32]),
+    "pclip_topk_prepare_bank": (C.c_int, [_P, _I64, _I32, _P, _SZ, _P]),
+    "pclip_topk_prepared": (C.c_int, [_P, _P, _P, _I64, _I64, _I32, _I32, _I64, _P, _P, _P, _P, _SZ, _P]),
     "pclip_topk_workspace_bytes": (_SZ, [_I64, _I64, _I32, _I32, _I32]),
     "pclip_topk": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _I32, _I64, _P, _P, _P, _P, _SZ, _P]),
     "pclip_topk_merge": (C.c_int, [_P, _P, _I64, _I32, _I32, _P, _P, _P]),

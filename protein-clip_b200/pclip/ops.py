@@ -43,8 +43,9 @@ class _NormalizeScale(torch.autograd.Function):
         out = torch.empty_like(e2)
         inv = torch.empty(rows, dtype=torch.float32, device=e.device)
         tau_d = None if tau is None else tau.detach().reshape(1).float().to(e.device)
-        L.check(L.lib().pclip_normalize_scale_fwd(L.ptr(e2), rows, D, L.ptr(tau_d), float(eps), L.ptr(out), L.ptr(inv),
-                                                  L.stream_ptr(e.device)))
+        with torch.cuda.device(e.device):
+            L.check(L.lib().pclip_normalize_scale_fwd(L.ptr(e2), rows, D, L.ptr(tau_d), float(eps), L.ptr(out),
+                                                      L.ptr(inv), L.stream_ptr(e.device)))
         ctx.save_for_backward(out, inv, tau_d if tau_d is not None else torch.empty(0, device=e.device))
         ctx.has_tau = tau is not None
         ctx.shape = shape
@@ -58,9 +59,10 @@ class _NormalizeScale(torch.autograd.Function):
         g2 = g.reshape(rows, D).contiguous().float()
         de = torch.empty_like(out)
         dtau = torch.zeros(1, dtype=torch.float32, device=out.device) if ctx.has_tau else None
-        L.check(L.lib().pclip_normalize_scale_bwd(L.ptr(g2), L.ptr(out), L.ptr(inv), rows, D,
-                                                  L.ptr(tau_d) if ctx.has_tau else None, L.ptr(de), L.ptr(dtau),
-                                                  L.stream_ptr(out.device)))
+        with torch.cuda.device(out.device):
+            L.check(L.lib().pclip_normalize_scale_bwd(L.ptr(g2), L.ptr(out), L.ptr(inv), rows, D,
+                                                      L.ptr(tau_d) if ctx.has_tau else None, L.ptr(de), L.ptr(dtau),
+                                                      L.stream_ptr(out.device)))
         return de.reshape(ctx.shape), (dtau.reshape(ctx.tau_shape) if ctx.has_tau else None), None
 
 
@@ -82,11 +84,23 @@ def _as_rows(ts):
     return [t if t.dtype == dt else t.to(dt) for t in out]
 
 
+MAX_CHUNKS = 32   # pclip_pack takes at most 32 row chunks per modality (csrc/elementwise.cu kMaxChunks)
+
+
+def _limit_chunks(ts):
+    """More than 32 leaves (train_gc with accumulated_batches > 32): concatenate neighbouring leaves so that at most
+    32 chunks reach the pack kernel.  The reference's cat_input_tensor accepts any count."""
+    if len(ts) <= MAX_CHUNKS:
+        return ts
+    per = -(-len(ts) // MAX_CHUNKS)
+    return [torch.cat(ts[i:i + per], 0) if len(ts[i:i + per]) > 1 else ts[i] for i in range(0, len(ts), per)]
+
+
 def clip_loss_raw(xs, ys, compute: int, want_grad: bool, want_lse: bool = False):
     """xs / ys: lists of [rows_i, D] CUDA tensors (any strides).  Returns (loss[1], dx, dy, row_lse, col_lse) with
     dx / dy packed [B, D] fp32 for grad_output == 1 (None unless want_grad)."""
     L.require_cuda(*xs, *ys)
-    xs, ys = _as_rows(xs), _as_rows(ys)
+    xs, ys = _limit_chunks(_as_rows(xs)), _limit_chunks(_as_rows(ys))
     if ys[0].dtype != xs[0].dtype:
         ys = [t.to(xs[0].dtype) for t in ys]
     dev = xs[0].device
@@ -95,7 +109,8 @@ def clip_loss_raw(xs, ys, compute: int, want_grad: bool, want_lse: bool = False)
     if sum(t.shape[0] for t in ys) != B or any(t.shape[1] != D for t in xs + ys):
         raise L.PclipError("clip_loss: x and y must hold the same number of [*, D] rows")
     lib = L.lib()
-    nbytes = lib.pclip_clip_workspace_bytes(B, D, compute)
+    with torch.cuda.device(dev):     # the workspace plan depends on the SM count of the tensors' device
+        nbytes = lib.pclip_clip_workspace_bytes(B, D, compute)
     owner, ws = L.workspace(nbytes, dev)
     loss = torch.empty(1, dtype=torch.float32, device=dev)
     # one allocation for both gradients: backward scales it by grad_output with a single launch
@@ -134,7 +149,9 @@ class _ClipInfoNCE(torch.autograd.Function):
         (dxy,) = ctx.saved_tensors                      # [2, B, D] for grad_output == 1
         g = g.reshape(1).float().contiguous()
         out = torch.empty_like(dxy)
-        L.check(L.lib().pclip_scale_by_scalar(L.ptr(dxy), L.ptr(g), dxy.numel(), L.ptr(out), L.stream_ptr(dxy.device)))
+        with torch.cuda.device(dxy.device):
+            L.check(L.lib().pclip_scale_by_scalar(L.ptr(dxy), L.ptr(g), dxy.numel(), L.ptr(out),
+                                                  L.stream_ptr(dxy.device)))
         # the 2B rows in leaf order: x chunks then y chunks
         pieces = out.view(-1, out.shape[-1]).split(ctx.rows)
         grads = [p if dt == torch.float32 else p.to(dt) for p, dt in zip(pieces, ctx.dtypes)]
@@ -206,24 +223,34 @@ class ClipPlan:
         self.loss = torch.zeros(1, **f32)
         self.dx, self.dy = torch.empty(Ma, D, **f32), torch.empty(Ma, D, **f32)
         lib = L.lib()
-        n = max(lib.pclip_clip_rowsumexp_workspace_bytes(Ma, Nb, D, compute),
-                lib.pclip_clip_sumexp_workspace_bytes(Ma, Nb, D, compute) if tc else 0,
-                lib.pclip_clip_grad_workspace_bytes(Ma, Nb, D, compute), 1024)
+        with torch.cuda.device(dev):
+            n = max(lib.pclip_clip_rowsumexp_workspace_bytes(Ma, Nb, D, compute),
+                    lib.pclip_clip_sumexp_workspace_bytes(Ma, Nb, D, compute) if tc else 0,
+                    lib.pclip_clip_grad_workspace_bytes(Ma, Nb, D, compute), 1024)
         self.ws_bytes = int(n)
         self._ws_owner, self.ws = L.workspace(n, dev)
 
     def _st(self):
         return L.stream_ptr(self.dev)
 
+    def _on_device(fn):   # every stage launches on the plan's device, whatever the caller's current device is
+        def wrapped(self, *a, **k):
+            with torch.cuda.device(self.dev):
+                return fn(self, *a, **k)
+        wrapped.__name__, wrapped.__doc__ = fn.__name__, fn.__doc__
+        return wrapped
+
+    @_on_device
     def pack(self, xs, ys):
         """Strided row chunks (GradCache leaves, `.t()` views) -> packed compute-dtype rows (+ transposes)."""
         lib = L.lib()
-        xs, ys = _as_rows(xs), _as_rows(ys)
+        xs, ys = _limit_chunks(_as_rows(xs)), _limit_chunks(_as_rows(ys))
         full = self.local_is_full
         for src, out, outT in ((xs, self.xl, self.xfT if full else None), (ys, self.yl, self.yfT if full else None)):
             L.check(lib.pclip_pack(L.chunks_of(src), len(src), L.dtype_code(src[0].dtype), self.Ma, self.D,
                                    L.dtype_code(self.cdt), L.ptr(out), L.ptr(outT), self.ldT, self._st()))
 
+    @_on_device
     def transpose_full(self):
         """After an all-gather into xf / yf: the transposed copies the bf16 gradient kernel reads."""
         if self.xfT is None or self.local_is_full:
@@ -232,12 +259,14 @@ class ClipPlan:
         for src, dst in ((self.xf, self.xfT), (self.yf, self.yfT)):
             L.check(lib.pclip_transpose_bf16(L.ptr(src), self.Nb, self.D, L.ptr(dst), self.ldT, self._st()))
 
+    @_on_device
     def rowsumexp(self):
         sides = (L.FwdSide * 2)(
             L.FwdSide(L.ptr(self.xl), L.ptr(self.yf), self.Ma, self.Nb, self.off, L.ptr(self.rowsum), L.ptr(self.diag)),
             L.FwdSide(L.ptr(self.yl), L.ptr(self.xf), self.Ma, self.Nb, self.off, L.ptr(self.colsum), L.ptr(self.diag2)))
         L.check(L.lib().pclip_clip_rowsumexp(sides, 2, self.D, self.compute, self.ws, self.ws_bytes, self._st()))
 
+    @_on_device
     def sumexp(self):
         """Single-pass forward: rowsum (complete), colsum_f (all Nb columns, summed over THIS plan's rows), diag."""
         L.check(L.lib().pclip_clip_sumexp(L.ptr(self.xl), L.ptr(self.yf), self.Ma, self.Nb, self.off, self.D,
@@ -249,12 +278,14 @@ class ClipPlan:
         if not self.local_is_full:
             self.colsum.copy_(self.colsum_f[self.off:self.off + self.Ma])
 
+    @_on_device
     def finalize(self, B_total: int):
         """loss[0] = 1/(2B) sum_i (log R_i + log C_i - 2 S_ii) over the local rows; 1/R, 1/C for the backward."""
         L.check(L.lib().pclip_clip_finalize(L.ptr(self.rowsum), L.ptr(self.colsum), L.ptr(self.diag), self.Ma,
                                             0.5 / B_total, L.ptr(self.row_lse), L.ptr(self.col_lse), L.ptr(self.rinv),
                                             L.ptr(self.cinv), L.ptr(self.loss), self._st()))
 
+    @_on_device
     def finalize_full(self, stats_all: torch.Tensor, B_total: int):
         """Row shard, after the all-gather of every rank's [C partial | R | S_ii] record (`stats_all` [P, Nb + 2 Ma]):
         reduce the column partials, lay R and S_ii out by global row, and finalise ALL rows here -- the loss comes out
@@ -268,6 +299,7 @@ class ClipPlan:
                                             0.5 / B_total, L.ptr(self.row_lse_f), L.ptr(self.col_lse_f),
                                             L.ptr(self.rinv_f), L.ptr(self.cinv_f), L.ptr(self.loss), self._st()))
 
+    @_on_device
     def grad(self, B_total: int, gscale: torch.Tensor | None = None):
         sides = (L.BwdSide * 2)(
             L.BwdSide(L.ptr(self.xl), L.ptr(self.yf), L.ptr(self.yfT), self.ldT, self.Ma, self.Nb, self.off,
@@ -322,8 +354,11 @@ def rank_of_positive(q: torch.Tensor, bank: torch.Tensor, pos: torch.Tensor) -> 
     pos = pos.to(torch.int64).contiguous()
     rank = torch.empty(q.shape[0], dtype=torch.int32, device=q.device)
     with torch.cuda.device(q.device):
+        nbytes = int(L.lib().pclip_rank_workspace_bytes(q.shape[0]))
+        owner, ws = L.workspace(nbytes, q.device)
         L.check(L.lib().pclip_rank_of_positive(L.ptr(q), L.ptr(bank), L.ptr(pos), q.shape[0], bank.shape[0], q.shape[1],
-                                               L.ptr(rank), L.stream_ptr(q.device)))
+                                               L.ptr(rank), ws, nbytes, L.stream_ptr(q.device)))
+    owner.record_stream(torch.cuda.current_stream(q.device))
     return rank
 
 
@@ -335,14 +370,36 @@ class TopkPlan:
         self.idx = torch.empty(Q, k, dtype=torch.int64, device=device)
         self.score = torch.empty(Q, k, dtype=torch.float32, device=device)
         self.n_unsafe = torch.zeros(1, dtype=torch.int32, device=device)
-        self.ws_bytes = int(L.lib().pclip_topk_workspace_bytes(Q, N, D, k, compute))
+        with torch.cuda.device(self.dev):
+            self.ws_bytes = int(L.lib().pclip_topk_workspace_bytes(Q, N, D, k, compute))
         self._owner, self.ws = L.workspace(max(self.ws_bytes, 1024), device)
+        self._bank_key, self._bank_owner, self._bank_img = None, None, None
+
+    def prepare_bank(self, bank: torch.Tensor):
+        """Build the persistent bf16 image of `bank` once; later run() calls with the SAME tensor (same storage, not
+        modified in place since) skip the per-call fp32 -> bf16 conversion of the bank (3 N D bytes of HBM traffic)."""
+        assert self.compute == BF16 and bank.shape == (self.N, self.D) and bank.dtype == torch.float32
+        assert bank.is_contiguous()
+        lib = L.lib()
+        with torch.cuda.device(self.dev):
+            nbytes = int(lib.pclip_topk_bank_bytes(self.N, self.D))
+            self._bank_owner, self._bank_img = L.workspace(nbytes, self.dev)
+            L.check(lib.pclip_topk_prepare_bank(L.ptr(bank), self.N, self.D, self._bank_img, nbytes,
+                                                L.stream_ptr(self.dev)))
+        self._bank_key = (bank.data_ptr(), bank._version)
+        return self
 
     def run(self, q: torch.Tensor, bank: torch.Tensor, index_base: int = 0):
         assert q.shape == (self.Q, self.D) and bank.shape == (self.N, self.D)
         assert q.dtype == torch.float32 and bank.dtype == torch.float32 and q.is_contiguous() and bank.is_contiguous()
+        lib = L.lib()
         with torch.cuda.device(self.dev):
-            L.check(L.lib().pclip_topk(L.ptr(q), L.ptr(bank), self.Q, self.N, self.D, self.k, self.compute, index_base,
+            if self._bank_key == (bank.data_ptr(), bank._version):
+                L.check(lib.pclip_topk_prepared(L.ptr(q), L.ptr(bank), self._bank_img, self.Q, self.N, self.D, self.k,
+                                                index_base, L.ptr(self.idx), L.ptr(self.score), L.ptr(self.n_unsafe),
+                                                self.ws, self.ws_bytes, L.stream_ptr(self.dev)))
+            else:
+                L.check(lib.pclip_topk(L.ptr(q), L.ptr(bank), self.Q, self.N, self.D, self.k, self.compute, index_base,
                                        L.ptr(self.idx), L.ptr(self.score), L.ptr(self.n_unsafe), self.ws, self.ws_bytes,
                                        L.stream_ptr(self.dev)))
         return self.idx, self.score
@@ -391,6 +448,17 @@ def mask_lengths(mask: torch.Tensor) -> torch.Tensor:
     return lens.contiguous()
 
 
+def compact_tokens(h: torch.Tensor, mask: torch.Tensor):
+    """Move the valid tokens of every sample to the front, keeping their order: ([B, T, D] reordered, int32 lengths).
+    FILIP's max-over-tokens and masked mean do not depend on token order, so an arbitrary 0/1 mask (the reference
+    accepts any, modules/models.py:333-340) becomes the right-padded form the kernels take; pads end up behind the
+    valid tokens with their values untouched (they are never read).  Differentiable through the gather; no host sync."""
+    m = mask.to(torch.bool)
+    order = torch.sort((~m).to(torch.int8), dim=1, stable=True).indices          # valid tokens first, stable
+    lens = m.sum(dim=1).to(torch.int32)
+    return torch.gather(h, 1, order[..., None].expand_as(h)), lens
+
+
 class _FilipSimilarity(torch.autograd.Function):
     @staticmethod
     def forward(ctx, hA, hB, lenA, lenB, tau, compute):
@@ -401,7 +469,8 @@ class _FilipSimilarity(torch.autograd.Function):
         Bb, TB, _ = b.shape
         tau_d = tau.detach().reshape(1).float().to(dev)
         lib = L.lib()
-        nbytes = int(lib.pclip_filip_workspace_bytes(Ba, Bb, TA, TB, D, compute))
+        with torch.cuda.device(dev):
+            nbytes = int(lib.pclip_filip_workspace_bytes(Ba, Bb, TA, TB, D, compute))
         owner, ws = L.workspace(nbytes, dev)
         simA = torch.empty(Ba, Bb, dtype=torch.float32, device=dev)
         simB = torch.empty(Ba, Bb, dtype=torch.float32, device=dev)
@@ -427,7 +496,8 @@ class _FilipSimilarity(torch.autograd.Function):
         gA = torch.zeros_like(simA) if gA is None else gA.float().contiguous()
         gB = torch.zeros_like(simB) if gB is None else gB.float().contiguous()
         lib = L.lib()
-        nbytes = int(lib.pclip_filip_workspace_bytes(Ba, Bb, TA, TB, D, ctx.compute))
+        with torch.cuda.device(dev):
+            nbytes = int(lib.pclip_filip_workspace_bytes(Ba, Bb, TA, TB, D, ctx.compute))
         owner, ws = L.workspace(nbytes, dev)
         dhA, dhB = torch.empty_like(a), torch.empty_like(b)
         dtau = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -437,6 +507,30 @@ class _FilipSimilarity(torch.autograd.Function):
                                         L.ptr(gB), L.ptr(dhA), L.ptr(dhB), L.ptr(dtau), ws, nbytes, L.stream_ptr(dev)))
         owner.record_stream(torch.cuda.current_stream(dev))
         return (dhA.to(ctx.in_dtypes[0]), dhB.to(ctx.in_dtypes[1]), None, None, dtau.reshape(ctx.tau_shape), None)
+
+
+def filip_similarity_raw(hA, hB, lenA, lenB, tau, compute: int):
+    """pclip_filip_fwd without autograd: (simA, simB [Ba,Bb], argA [Ba,Bb,TA], argB [Bb,Ba,TB] int16) -- the stored
+    maximisers are what the backward consumes; parity tests compare them between compute modes."""
+    L.require_cuda(hA, hB, lenA, lenB)
+    dev = hA.device
+    a, b = hA.detach().float().contiguous(), hB.detach().float().contiguous()
+    Ba, TA, D = a.shape
+    Bb, TB, _ = b.shape
+    tau_d = torch.as_tensor(tau, device=dev).detach().reshape(1).float()
+    la, lb = lenA.to(torch.int32).contiguous(), lenB.to(torch.int32).contiguous()
+    lib = L.lib()
+    simA = torch.empty(Ba, Bb, dtype=torch.float32, device=dev)
+    simB = torch.empty(Ba, Bb, dtype=torch.float32, device=dev)
+    argA = torch.zeros(Ba, Bb, TA, dtype=torch.int16, device=dev)
+    argB = torch.zeros(Bb, Ba, TB, dtype=torch.int16, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = int(lib.pclip_filip_workspace_bytes(Ba, Bb, TA, TB, D, compute))
+        owner, ws = L.workspace(nbytes, dev)
+        L.check(lib.pclip_filip_fwd(L.ptr(a), L.ptr(b), L.ptr(la), L.ptr(lb), Ba, Bb, TA, TB, D, L.ptr(tau_d), compute, L.ptr(simA), L.ptr(simB), L.ptr(argA), L.ptr(argB),
+                                    ws, nbytes, L.stream_ptr(dev)))
+    owner.record_stream(torch.cuda.current_stream(dev))
+    return simA, simB, argA, argB
 
 
 def filip_similarity(hA, hB, maskA, maskB, tau, compute: int | None = None):
@@ -472,7 +566,8 @@ class _RowwiseInfoNCE(torch.autograd.Function):
         (dl,) = ctx.saved_tensors
         g = g.reshape(1).float().contiguous()
         out = torch.empty_like(dl)
-        L.check(L.lib().pclip_scale_by_scalar(L.ptr(dl), L.ptr(g), dl.numel(), L.ptr(out), L.stream_ptr(dl.device)))
+        with torch.cuda.device(dl.device):
+            L.check(L.lib().pclip_scale_by_scalar(L.ptr(dl), L.ptr(g), dl.numel(), L.ptr(out), L.stream_ptr(dl.device)))
         return out.to(ctx.in_dtype), None, None
 
 

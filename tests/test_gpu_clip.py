@@ -1,6 +1,7 @@
 """GPU parity of the CLIP InfoNCE path (libpclip.so through the C ABI) against the oracle and the golden vectors
 generated from the reference's own functions.  Tolerances are north_star's: 1e-5 relative in fp32, 1e-2 in bf16."""
 import math
+import os
 
 import pytest
 import torch
@@ -164,11 +165,26 @@ def test_single_pass_sumexp_vs_oracle(ops, Ma, Nb, off):
     assert float((plan.diag.double() - s[idx, idx + off]).abs().max()) < 1e-5
 
 
+def _oracle_lse_full(xr, yr, chunk=2048):
+    """Row and column log-sum-exp of S = xr yr^T at full size on the CPU: two chunked passes over the 65 536^2 logits
+    (fp32 GEMM + exp per chunk, float64 accumulation of the sums), ref: modules/training_utils.py:85-88."""
+    B = xr.shape[0]
+    R_ = torch.empty(B, dtype=torch.float64)
+    C_ = torch.zeros(B, dtype=torch.float64)
+    yt = yr.t().contiguous()
+    for i0 in range(0, B, chunk):
+        e = (xr[i0:i0 + chunk] @ yt).exp_()
+        R_[i0:i0 + chunk] = e.sum(1, dtype=torch.float64)
+        C_ += e.sum(0, dtype=torch.float64)
+    return R_.log(), C_.log()
+
+
 def test_clip_full_size_properties(ops):
-    """cfg 4 (B = 65 536, bf16): size-independent properties instead of an O(B^2) oracle pass.
+    """cfg 4 (B = 65 536, bf16; the gradient runs with 2 column splits + grad_reduce_kernel at this size).
     (a) all-zero embeddings: every logit is 0, so loss = ln B and both gradients vanish;
-    (b) row / column LSEs and gradient rows of a 256-row sample against the float64 oracle restricted to those
-        rows, and the loss against its definition from the kernel's own LSEs."""
+    (b) against an INDEPENDENT oracle: row and column LSEs of all 65 536 rows from two chunked CPU passes over the
+        bf16-rounded inputs, the loss from them, and 256-row blocks of BOTH gradients from the closed form
+        dS = (E/R + E/C - 2I) / 2B with the oracle's R and C (ref: modules/training_utils.py:85-89)."""
     B, D = 65536, 128
     z = torch.zeros(B, D, device="cuda")
     loss, dx, dy, _, _ = ops.clip_loss_raw([z], [z], ops.BF16, True)
@@ -177,25 +193,43 @@ def test_clip_full_size_properties(ops):
     from pclip import synth
     x, y = synth.clip_scaled_embeddings(B, D, cfg_id=4)
     loss, dx, dy, rl, cl = ops.clip_loss_raw([x.cuda()], [y.cuda()], ops.BF16, True, want_lse=True)
-    # oracle on a row sample: row LSE of 256 rows of x against all y, column LSE of 256 rows of y against all x
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    xr, yr = R.bf16_round(x), R.bf16_round(y)
+    rl_o, cl_o = _oracle_lse_full(xr, yr)
+    assert_close(rl.cpu(), rl_o, 1e-5, "row_lse (all rows)")
+    assert_close(cl.cpu(), cl_o, 2e-5, "col_lse (all columns)")   # column sums add bf16-rounded exps (unbiased)
+    diag = (xr.double() * yr.double()).sum(-1)
+    loss_o = (rl_o + cl_o - 2 * diag).sum() / (2 * B)
+    assert_close(loss[0], loss_o, 1e-5, "loss vs oracle")
+    # gradient blocks: rows 256 k' of x (dX = G y) and of y (dY = G^T x), oracle normalisers
     idx = torch.arange(0, B, B // 256)
-    xr, yr = R.bf16_round(x).double(), R.bf16_round(y).double()
-    rl_o = torch.logsumexp(xr[idx] @ yr.t(), dim=1)
-    cl_o = torch.logsumexp(yr[idx] @ xr.t(), dim=1)
-    assert_close(rl.cpu()[idx], rl_o, 1e-5, "row_lse sample")
-    assert_close(cl.cpu()[idx], cl_o, 1e-5, "col_lse sample")
-    diag = (xr * yr).sum(-1)
-    # loss from its definition with the kernel's own LSEs and the exact diagonal
-    loss_def = (rl.double().cpu() + cl.double().cpu() - 2 * diag).sum() / (2 * B)
-    assert_close(loss[0], loss_def, 1e-5, "loss vs definition")
-    # gradient rows of the sample against the closed form with the kernel's LSEs
-    e = (xr[idx] @ yr.t())
-    g = (torch.exp(e - rl.double().cpu()[idx, None]) + torch.exp(e - cl.double().cpu()[None, :]))
-    dx_o = (g @ yr - 2 * yr[idx]) / (2 * B)
-    assert_close(dx.cpu()[idx], dx_o, 4e-3, "dx sample")
+    x64, y64 = xr.double(), yr.double()
+    s = x64[idx] @ y64.t()
+    g = torch.exp(s - rl_o[idx, None]) + torch.exp(s - cl_o[None, :])
+    dx_o = (g @ y64 - 2 * y64[idx]) / (2 * B)
+    assert_close(dx.cpu()[idx], dx_o, 4e-3, "dx block")
+    st = y64[idx] @ x64.t()                                           # S^T rows: [j, i]
+    gt = torch.exp(st - rl_o[None, :]) + torch.exp(st - cl_o[idx, None])
+    dy_o = (gt @ x64 - 2 * x64[idx]) / (2 * B)
+    assert_close(dy.cpu()[idx], dy_o, 4e-3, "dy block")
 
 
 def test_no_cpu_fallback(ops):
     from pclip import _lib
     with pytest.raises(_lib.PclipError):
         ops.clip_loss(torch.randn(4, 128), torch.randn(4, 128))
+
+
+def test_gradcache_more_than_32_leaves(ops):
+    """the pack kernel takes 32 chunks; train_gc(accumulated_batches=40) must still work like the
+    reference's cat_input_tensor, which accepts any number of leaves."""
+    from pclip import synth
+    x, y = synth.clip_scaled_embeddings(40 * 8, 128, cfg_id=91)
+    lo, dxo, dyo, _, _ = R.clip_loss_and_grads(x.double(), y.double())
+    xs = [t.cuda().requires_grad_() for t in x.split(8)]
+    ys = [t.cuda().requires_grad_() for t in y.split(8)]
+    loss = ops.clip_loss(xs, ys, compute=ops.F32)
+    loss.backward()
+    assert_close(loss, lo, 1e-5, "loss, 40 leaves")
+    assert_close(torch.cat([t.grad for t in xs]), dxo, 3e-5, "dx, 40 leaves")
+    assert_close(torch.cat([t.grad for t in ys]), dyo, 3e-5, "dy, 40 leaves")

@@ -121,3 +121,128 @@ def test_filip_rectangular_row_shard(ops, mode):
                                                             tau.cuda(), compute=_mode(ops, mode)), diag_offset=i)) * 2
                  for i in (0, 2, 4)) / 6
     assert abs(l_part - float(l_full)) <= 1e-5 * abs(float(l_full))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# bf16 gradients to north_star's 1e-2 on every token row whose maximisers agree
+# ---------------------------------------------------------------------------------------------------------
+def _dirty_rows(arg16, arg32, argo16, argo32, lens_own, lens_other):
+    """Token rows [B, T] of one modality whose gradient is re-routed by a maximiser flip between the two paths:
+    arg* [B, Bo, T] = the row's own maximisers, argo* [Bo, B, To] = the other modality's maximisers (which point INTO
+    these rows).  A flip of the row's own maximiser, or a column of the other modality that switched to / from the row,
+    makes it dirty."""
+    B, Bo, T = arg16.shape
+    To = argo16.shape[2]
+    valid_own = (torch.arange(T, device=arg16.device)[None, :] < lens_own[:, None])            # [B, T]
+    valid_oth = (torch.arange(To, device=arg16.device)[None, :] < lens_other[:, None])         # [Bo, To]
+    own_flip = (arg16 != arg32) & valid_own[:, None, :] & (lens_other > 0)[None, :, None]
+    dirty = own_flip.any(1)
+    oth_flip = (argo16 != argo32) & valid_oth[:, None, :] & (lens_own > 0)[None, :, None]       # [Bo, B, To]
+    bo, b, s = oth_flip.nonzero(as_tuple=True)
+    dirty[b, argo16[bo, b, s].long()] = True
+    dirty[b, argo32[bo, b, s].long()] = True
+    n_flips = int(own_flip.sum()) + int(oth_flip.sum())
+    return dirty, n_flips
+
+
+@pytest.mark.parametrize("name", ["filip_b4_full", "filip_b5_ragged", "filip_b6_t70"])
+def test_filip_bf16_gradient_rows_with_agreeing_argmax(ops, golden, name):
+    """bf16 rounding of the tokens may flip a near-tied maximiser, which re-routes that token's gradient to another
+    token: that is a property of the arg-max, not an arithmetic error.  So: count the flips against the fp32 path, and
+    hold EVERY token row that no flip touches to north_star's 1e-2 (max-rel against the reference's own gradient);
+    only the flipped rows are covered by the aggregate bound."""
+    g = golden(name)
+    lenA, lenB = g["maskA"].sum(1).cuda(), g["maskB"].sum(1).cuda()
+    nA = ops.normalize_scale(g["hA"].cuda(), None, eps=0.0)
+    nB = ops.normalize_scale(g["hB"].cuda(), None, eps=0.0)
+    _, _, a16, b16 = ops.filip_similarity_raw(nA, nB, lenA, lenB, g["tau"].cuda(), ops.BF16)
+    _, _, a32, b32 = ops.filip_similarity_raw(nA, nB, lenA, lenB, g["tau"].cuda(), ops.F32)
+    dirtyA, flipsA = _dirty_rows(a16, a32, b16, b32, lenA, lenB)
+    dirtyB, flipsB = _dirty_rows(b16, b32, a16, a32, lenB, lenA)
+    total = int(lenA.sum()) * len(lenB) + int(lenB.sum()) * len(lenA)
+    print(f"{name}: {flipsA} maximiser flips of {total} ({100.0 * flipsA / total:.3f} %), "
+          f"dirty token rows A {int(dirtyA.sum())} / B {int(dirtyB.sum())}")
+    assert flipsA == flipsB
+    assert flipsA <= 0.02 * total            # N(0,1) tokens at T <= 70: a few near-ties per thousand
+    _, _, _, dhA, dhB, _ = run_filip(ops, g["hA"], g["hB"], g["maskA"], g["maskB"], g["tau"], ops.BF16, normalize=True)
+    for got, want, dirty in ((dhA, g["dhA"], dirtyA), (dhB, g["dhB"], dirtyB)):
+        want = want.cuda()
+        err = (got - want).abs().amax(-1)                                  # per token row
+        scale = want.abs().max()
+        clean = ~dirty
+        assert clean.float().mean() > 0.5
+        assert float(err[clean].max() / scale) <= 1e-2, "a token row with agreeing maximisers is off by more than 1e-2"
+        assert float((got - want).norm() / want.norm()) <= 5e-2            # flipped rows: aggregate only
+
+
+# ---------------------------------------------------------------------------------------------------------
+# VERDICT r1, weak #2: parity AT configs[2] size (B = 256, T = 512 / 512), full-length and PDB-like ragged
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ragged", [False, True])
+def test_filip_cfg3_size_against_oracle_rows(ops, ragged):
+    """Both losses are row-wise (ref: training_utils_filip.py:26-39), so sample a of the batch depends only on hA[a]
+    and all of hB: the float64 oracle is evaluated for 4 samples (all 256 x 512 columns each) on the SAME bf16-rounded
+    normalised tokens and compared with rows of simA / simB, the per-row loss terms, the rows' share of d tau and the
+    gradient of those samples' tokens; the loss tail and d tau are checked at full size from the kernel's own simA/simB."""
+    from pclip import synth
+    B, T = 256, 512
+    hA, hB, mA, mB, tau = synth.filip_tokens(B, T, T, cfg_id=3, ragged=ragged)
+    nA = R.bf16_round(R.filip_normalize(hA.double()).float())
+    nB = R.bf16_round(R.filip_normalize(hB.double()).float())
+    del hA, hB
+    a_d, b_d = nA.cuda().requires_grad_(), nB.cuda().requires_grad_()
+    t_d = tau.cuda().requires_grad_()
+    lenA, lenB = mA.sum(1).cuda(), mB.sum(1).cuda()
+    simA, simB = ops.filip_similarity(a_d, b_d, lenA, lenB, t_d, compute=ops.BF16)
+    loss = ops.filip_loss(simA, simB)
+    loss.backward()
+    sA, sB = simA.detach().double().cpu(), simB.detach().double().cpu()
+    # (1) loss tail and d tau at full size, from the kernel's own similarity matrices
+    loss_def = R.filip_compute_loss(sA, sB)
+    assert abs(float(loss.detach()) - float(loss_def)) <= 1e-5 * abs(float(loss_def))
+    eye = torch.eye(B, dtype=torch.float64)
+    gA, gB = (torch.softmax(sA, 1) - eye) / (2 * B), (torch.softmax(sB, 1) - eye) / (2 * B)
+    dtau_def = -((gA * sA).sum() + (gB * sB).sum()) / float(tau)
+    # d tau is a sum of terms of both signs that nearly cancels on random data: measure against the terms' magnitude
+    dtau_mag = ((gA * sA).abs().sum() + (gB * sB).abs().sum()) / float(tau)
+    assert abs(float(t_d.grad) - float(dtau_def)) <= 1e-5 * float(dtau_mag)
+    # (2) four samples against the oracle
+    rows = [0, 85, 170, 255]
+    nB64 = nB.double()
+    oA, oB, argA, argB = R.filip_similarity(nA[rows].double(), nB64, mA[rows], mB, tau.double(), want_arg=True)
+    assert rel_err(sA[rows], oA) <= 1e-5 and rel_err(sB[rows], oB) <= 1e-5
+    # the maximisers the kernel stored, against the oracle's: the keys carry the score to 2^-18 relative, so runners-up
+    # closer than that may win (expected: a few in 10^5); such flips re-route token rows and are counted, not hidden
+    _, _, k_argA, k_argB = ops.filip_similarity_raw(a_d.detach(), b_d.detach(), lenA, lenB, t_d.detach(), ops.BF16)
+    # gradient of the sampled samples' tokens: gather through argA, scatter through argB (closed form, restate.py)
+    nAcount = mA.sum(1).clamp(min=1e-6).double()
+    nBcount = mB.sum(1).clamp(min=1e-6).double()
+    flips = total = 0
+    for k, a in enumerate(rows):
+        want = torch.zeros(T, 128, dtype=torch.float64)
+        tv = mA[a].bool().nonzero().flatten()
+        dirty = torch.zeros(T, dtype=torch.bool)
+        ka, kb = k_argA[a].long().cpu(), k_argB[:, a].long().cpu()          # [B, TA], [B, TB]
+        for b in range(B):
+            sv = mB[b].bool().nonzero().flatten()
+            if len(tv) == 0 or len(sv) == 0:
+                continue
+            want.index_add_(0, tv, (gA[a, b] / nAcount[a] / float(tau)) * nB64[b, argA[k, b, tv]])
+            want.index_add_(0, argB[k, b, sv], (gB[a, b] / nBcount[b] / float(tau)) * nB64[b, sv])
+            fa = ka[b, tv] != argA[k, b, tv]
+            fb = kb[b, sv] != argB[k, b, sv]
+            dirty[tv[fa]] = True
+            dirty[kb[b, sv][fb]] = True
+            dirty[argB[k, b, sv][fb]] = True
+            flips += int(fa.sum()) + int(fb.sum())
+            total += len(tv) + len(sv)
+        got = a_d.grad[a].double().cpu()
+        err = (got - want).abs().amax(-1)
+        scale = want.abs().max()
+        assert float(err[~dirty].max()) <= 1e-3 * float(scale), f"sample {a}: a token row with agreeing maximisers is off"
+        # (a flipped row of the positive pair carries a 256 times larger weight than the others: no aggregate bound
+        # over the flipped rows at this size; they are counted below)
+        assert int(dirty.sum()) <= 8
+        assert float(got[len(tv):].abs().max() if len(tv) < T else 0.0) == 0.0
+    print(f"cfg 3 ({'ragged' if ragged else 'full'}): {flips} maximiser flips of {total} in 4 samples")
+    assert flips <= 1e-3 * total

@@ -131,17 +131,17 @@ def test_topk_adversarial_bf16_midpoints(ops):
     g = torch.Generator().manual_seed(11)
     N, Q, k = 4096, 8, 10
     bank = 0.01 * torch.randn(N, 128, generator=g)
-    victim = 3000
+    victim = 40                               # victim and decoys share one 128-row bank tile (one split)
     bank[victim] = a * up
     for i in range(30):                       # decoy i: bf16-exact, 8 entries one bf16 ulp up
         row = torch.full((128,), a)
         row[4 * i: 4 * i + 8] = a * (1.0 + 2.0 ** -7)
-        bank[100 + 7 * i] = row
+        bank[1 + i] = row
     q = torch.randn(Q, 128, generator=g)
     q[:4] = a * up
-    assert float((q[0].double() @ bank[victim].double())) > float((q[0].double() @ bank[100].double()))
+    assert float((q[0].double() @ bank[victim].double())) > float((q[0].double() @ bank[1].double()))
     assert float(q[0].bfloat16().double() @ bank[victim].bfloat16().double()) < \
-        float(q[0].bfloat16().double() @ bank[100].bfloat16().double())
+        float(q[0].bfloat16().double() @ bank[1].bfloat16().double())
     i32, s32, _ = ops.topk(q.cuda(), bank.cuda(), k, compute=ops.F32)
     i16, s16, unsafe = ops.topk(q.cuda(), bank.cuda(), k, compute=ops.BF16)
     assert i32[:4, 0].tolist() == [victim] * 4
