@@ -53,13 +53,16 @@ __device__ __forceinline__ float max3(float a, float b, float c) {
 // 1. fp32 [rows, 128] -> bf16 [rows, 128]; norm[r] = ||row r||_2 (optional); *maxnorm = max_r ||row r|| (optional,
 //    as an int-ordered float: norms are >= 0).  One warp per row, one float4 per lane.
 // ---------------------------------------------------------------------------------------------------------
+// Per row: bf16 copy, ||x|| (norm), ||x - bf16(x)|| (err), and for the bank the maxima over all rows of ||bf16(x)||
+// and of ||x - bf16(x)|| (max_bits[0], max_bits[1]; non-negative floats order like their bit patterns).  These are the
+// MEASURED rounding errors the exactness bound of topk_rescore_kernel is built from.
 __global__ void __launch_bounds__(256) to_bf16_norm_kernel(const float* __restrict__ in, int64_t rows,
                                                            __nv_bfloat16* __restrict__ out, float* __restrict__ norm,
-                                                           int* __restrict__ maxnorm_bits) {
+                                                           float* __restrict__ err, int* __restrict__ max_bits) {
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  float wmax = 0.f;
+  float wmax = 0.f, emax = 0.f;
   for (int64_t r = warp0; r < rows; r += nwarps) {
     const float4 v = *reinterpret_cast<const float4*>(in + r * tk::kDim + lane * 4);
     __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
@@ -67,14 +70,28 @@ __global__ void __launch_bounds__(256) to_bf16_norm_kernel(const float* __restri
     pk.x = *reinterpret_cast<uint32_t*>(&lo);
     pk.y = *reinterpret_cast<uint32_t*>(&hi);
     *reinterpret_cast<uint2*>(out + r * tk::kDim + lane * 4) = pk;
+    const float2 l2 = __bfloat1622float2(lo), h2 = __bfloat1622float2(hi);
     float s = v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    float sb = l2.x * l2.x + l2.y * l2.y + h2.x * h2.x + h2.y * h2.y;
+    const float dx = v.x - l2.x, dy = v.y - l2.y, dz = v.z - h2.x, dw = v.w - h2.y;   // exact in fp32
+    float se = dx * dx + dy * dy + dz * dz + dw * dw;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    const float n = sqrtf(s);
-    if (norm && lane == 0) norm[r] = n;
-    wmax = fmaxf(wmax, n);
+    for (int o = 16; o > 0; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      sb += __shfl_xor_sync(0xffffffffu, sb, o);
+      se += __shfl_xor_sync(0xffffffffu, se, o);
+    }
+    if (lane == 0) {
+      if (norm) norm[r] = sqrtf(s);
+      if (err) err[r] = sqrtf(se);
+    }
+    wmax = fmaxf(wmax, sqrtf(sb));
+    emax = fmaxf(emax, sqrtf(se));
   }
-  if (maxnorm_bits && lane == 0 && wmax > 0.f) atomicMax(maxnorm_bits, __float_as_int(wmax));
+  if (max_bits && lane == 0) {
+    if (wmax > 0.f) atomicMax(max_bits, __float_as_int(wmax));
+    if (emax > 0.f) atomicMax(max_bits + 1, __float_as_int(emax));
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -277,45 +294,115 @@ tc_topk_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
 // ---------------------------------------------------------------------------------------------------------
 // 3. exact re-scoring of the candidates + proof of exactness.  One warp per query.
 // ---------------------------------------------------------------------------------------------------------
-constexpr int kRescoreWarps = 8;
-constexpr int kMaxCandTotal = 512;  // nsplit * kc
+constexpr int kRescoreKeep = 64;      // candidates that get an fp32 score when a query has more than that many
+constexpr int kRescoreWarps = 8;      // at most; fewer when the candidate lists of a warp's query need more shared memory
+constexpr int kMaxCandTotal = 4096;   // nsplit * kc: up to 170 bank splits at kc = 24, so that a call with few queries
+                                      // (one query block) still spreads the bank over every SM
+
+// shared memory of one warp: its query (128 floats) and the re-scored candidates (score, index) of that query
+static size_t rescore_warp_bytes(int M) { return (size_t)tk::kDim * 4 + (size_t)M * 8 + (size_t)kRescoreKeep * 8; }
+static int rescore_warps(int M) {
+  return (int)std::max<size_t>(1, std::min<size_t>(kRescoreWarps, (size_t)96 * 1024 / rescore_warp_bytes(M)));
+}
 
 __global__ void __launch_bounds__(kRescoreWarps * 32)
 topk_rescore_kernel(const float* __restrict__ q, const float* __restrict__ bank, const int32_t* __restrict__ cand_idx,
                     const float* __restrict__ cand_score, const float* __restrict__ qnorm,
-                    const int* __restrict__ bmax_bits, int64_t Q, int nsplit, int kc, int k, int64_t index_base,
+                    const float* __restrict__ qerr, const int* __restrict__ bmax_bits, int64_t Q, int nsplit, int kc, int k, int64_t index_base,
                     int64_t* __restrict__ idx_out, float* __restrict__ score_out, int32_t* __restrict__ unsafe_list,
                     int32_t* __restrict__ unsafe_count) {
-  __shared__ float qs[kRescoreWarps][tk::kDim];
-  __shared__ float cs[kRescoreWarps][kMaxCandTotal];
-  __shared__ int32_t ci[kRescoreWarps][kMaxCandTotal];
+  extern __shared__ __align__(16) uint8_t rescore_smem[];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * kRescoreWarps + w;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + w;
   if (row >= Q) return;
   const int M = nsplit * kc;
-  *reinterpret_cast<float4*>(&qs[w][lane * 4]) = *reinterpret_cast<const float4*>(q + row * tk::kDim + lane * 4);
+  float* qs = reinterpret_cast<float*>(rescore_smem +
+                                       (size_t)w * ((size_t)tk::kDim * 4 + (size_t)M * 8 + (size_t)kRescoreKeep * 8));
+  float* cs = qs + tk::kDim;
+  int32_t* ci = reinterpret_cast<int32_t*>(cs + M);
+  *reinterpret_cast<float4*>(&qs[lane * 4]) = *reinterpret_cast<const float4*>(q + row * tk::kDim + lane * 4);
   __syncwarp();
   float tdisc = -FLT_MAX;  // largest bf16 score any discarded bank row can have
+  // (A) all candidates of the query with their bf16 scores; a full list's tail bounds what its split discarded
   for (int c = lane; c < M; c += 32) {
     const int s = c / kc, j = c - s * kc;
     const int64_t o = ((int64_t)s * Q + row) * kc + j;
     const int32_t id = cand_idx[o];
+    cs[c] = id >= 0 ? cand_score[o] : -FLT_MAX;
+    ci[c] = id >= 0 ? id : 0x7fffffff;
+    if (id >= 0 && j == kc - 1) tdisc = fmaxf(tdisc, cand_score[o]);
+  }
+  __syncwarp();
+  // (B) many bank splits (few queries per call): keep only the kRescoreKeep best candidates by bf16 score (ties: lower
+  //     index) for the fp32 pass -- the best score among the rest joins the discarded bound, so the proof below still
+  //     covers every bank row that is not re-scored.  Every split's list is sorted (best first), so this is a
+  //     tournament over the list heads: lane l owns the heads of splits l, l + 32, ...
+  int Mr = M;
+  if (M > kRescoreKeep) {
+    float* ks = reinterpret_cast<float*>(ci + M);
+    int32_t* ki = reinterpret_cast<int32_t*>(ks + kRescoreKeep);
+    constexpr int kHeads = (kMaxCandTotal / 16 + 31) / 32;      // splits per lane at the smallest list length
+    int hp[kHeads];
+#pragma unroll
+    for (int i = 0; i < kHeads; ++i) hp[i] = 0;
+    int kept = 0;
+    for (; kept < kRescoreKeep; ++kept) {
+      float bs = -FLT_MAX;
+      int32_t bi = 0x7fffffff;
+      int bsplit = -1;
+#pragma unroll
+      for (int i = 0; i < kHeads; ++i) {
+        const int sp = lane + 32 * i;
+        if (sp < nsplit && hp[i] < kc) {
+          const float sc = cs[sp * kc + hp[i]];
+          const int32_t id = ci[sp * kc + hp[i]];
+          if (id != 0x7fffffff && (bsplit < 0 || sc > bs || (sc == bs && id < bi))) bs = sc, bi = id, bsplit = sp;
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float os = __shfl_xor_sync(0xffffffffu, bs, o);
+        const int32_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        const int osp = __shfl_xor_sync(0xffffffffu, bsplit, o);
+        if (osp >= 0 && (bsplit < 0 || os > bs || (os == bs && oi < bi))) bs = os, bi = oi, bsplit = osp;
+      }
+      if (bsplit < 0) break;                   // all lists exhausted (warp-uniform)
+#pragma unroll
+      for (int i = 0; i < kHeads; ++i)
+        if (bsplit == lane + 32 * i) ++hp[i];
+      if (lane == 0) ks[kept] = bs, ki[kept] = bi;
+    }
+    // what was not kept: every split's remaining head is its best
+#pragma unroll
+    for (int i = 0; i < kHeads; ++i) {
+      const int sp = lane + 32 * i;
+      if (sp < nsplit && hp[i] < kc && ci[sp * kc + hp[i]] != 0x7fffffff) tdisc = fmaxf(tdisc, cs[sp * kc + hp[i]]);
+    }
+    __syncwarp();
+    for (int c = lane; c < kRescoreKeep; c += 32) {
+      cs[c] = c < kept ? ks[c] : -FLT_MAX;
+      ci[c] = c < kept ? ki[c] : 0x7fffffff;
+    }
+    __syncwarp();
+    Mr = kRescoreKeep;
+  }
+  // (C) exact fp32 scores of the kept candidates
+  for (int c = lane; c < Mr; c += 32) {
+    const int32_t id = ci[c];
     float acc = -FLT_MAX;
-    if (id >= 0) {
+    if (id != 0x7fffffff) {
       const float* b = bank + (int64_t)id * tk::kDim;
       acc = 0.f;
 #pragma unroll 4
       for (int d = 0; d < tk::kDim; d += 4) {  // the exact path's chain: ascending d, one FFMA per element
         const float4 bv = *reinterpret_cast<const float4*>(b + d);
-        acc = fmaf(qs[w][d], bv.x, acc);
-        acc = fmaf(qs[w][d + 1], bv.y, acc);
-        acc = fmaf(qs[w][d + 2], bv.z, acc);
-        acc = fmaf(qs[w][d + 3], bv.w, acc);
+        acc = fmaf(qs[d], bv.x, acc);
+        acc = fmaf(qs[d + 1], bv.y, acc);
+        acc = fmaf(qs[d + 2], bv.z, acc);
+        acc = fmaf(qs[d + 3], bv.w, acc);
       }
-      if (j == kc - 1) tdisc = fmaxf(tdisc, cand_score[o]);  // this split's list is full: its tail bounds the rest
     }
-    cs[w][c] = acc;
-    ci[w][c] = id >= 0 ? id : 0x7fffffff;
+    cs[c] = acc;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) tdisc = fmaxf(tdisc, __shfl_xor_sync(0xffffffffu, tdisc, o));
@@ -326,9 +413,9 @@ topk_rescore_kernel(const float* __restrict__ q, const float* __restrict__ bank,
     float bs = -FLT_MAX;
     int32_t bi = 0x7fffffff;
     int bc = -1;
-    for (int c = lane; c < M; c += 32) {
-      const float s = cs[w][c];
-      const int32_t id = ci[w][c];
+    for (int c = lane; c < Mr; c += 32) {
+      const float s = cs[c];
+      const int32_t id = ci[c];
       if (id != 0x7fffffff && (bc < 0 || s > bs || (s == bs && id < bi))) {
         bs = s;
         bi = id;
@@ -346,7 +433,7 @@ topk_rescore_kernel(const float* __restrict__ q, const float* __restrict__ bank,
         bc = oc;
       }
     }
-    if (bc >= 0 && (bc & 31) == lane) ci[w][bc] = 0x7fffffff;  // taken
+    if (bc >= 0 && (bc & 31) == lane) ci[bc] = 0x7fffffff;  // taken
     __syncwarp();
     if (lane == 0) {
       idx_out[row * k + p] = bc >= 0 ? (int64_t)bi + index_base : -1;
@@ -355,10 +442,15 @@ topk_rescore_kernel(const float* __restrict__ q, const float* __restrict__ bank,
     if (bc >= 0) kth = bs; else have_k = false;
   }
   if (lane == 0 && tdisc > -FLT_MAX) {
-    // bf16 has an 8-bit significand: round-to-nearest moves each operand by at most 2^-8 relative, so
-    // |bf16-path score - fp32-chain score| <= (2^-7 (1 + 2^-9) + D 2^-23) ||q|| ||b||  (Cauchy-Schwarz over the D
-    // products; fp32 accumulation on both sides); the factor 1.01 covers the second-order term with room to spare.
-    const float eps = (0.0078125f * 1.01f + 128.0f * 1.1920929e-7f) * qnorm[row] * __int_as_float(*bmax_bits);
+    // q.b - q^.b^ = q.(b - b^) + (q - q^).b^  (^ = rounded to bf16), so by Cauchy-Schwarz
+    //   |bf16-path score - fp32-chain score| <= ||q|| max||b - b^|| + ||q - q^|| max||b^|| + D 2^-23 ||q|| max||b^||
+    // with the rounding-error norms MEASURED when the operands were converted (to_bf16_norm_kernel) and the last term
+    // covering the fp32 accumulation on both sides.  The a-priori form of the same bound is 2^-7 (1 + 2^-9) ||q|| ||b||
+    // (each operand moves by at most 2^-8 relative; round 1 used half of that); the measured norms are
+    // ~2.4x smaller on random data, which keeps the exact-fallback list short.  1.001 absorbs the fp32 rounding of the
+    // norms themselves.
+    const float bhat = __int_as_float(bmax_bits[0]), berr = __int_as_float(bmax_bits[1]);
+    const float eps = 1.001f * (qnorm[row] * berr + qerr[row] * bhat) + 128.0f * 1.1920929e-7f * 1.01f * qnorm[row] * bhat;
     if (!have_k || !(kth > tdisc + eps)) unsafe_list[atomicAdd(unsafe_count, 1)] = (int32_t)row;
   }
 }
@@ -391,8 +483,8 @@ static void plan_topk_split(int64_t Q, int64_t N, int kc, int* nsplit, int* tps)
 
 struct TopkWs {
   __nv_bfloat16 *qb, *bb;
-  float* qnorm;
-  int32_t* scalars;  // [0] max bank norm bits, [1] unsafe count
+  float *qnorm, *qerr;
+  int32_t* scalars;  // [0] bits of max ||bf16(b)||, [1] bits of max ||b - bf16(b)||, [2] unsafe count
   int32_t* unsafe;
   int32_t* cand_idx;
   float* cand_score;
@@ -407,7 +499,8 @@ static TopkWs carve(void* ws, size_t ws_bytes, int64_t Q, int64_t N, int k, int 
   t.qb = w.take<__nv_bfloat16>((size_t)(Q + tk::kRows) * tk::kDim);
   t.bb = w.take<__nv_bfloat16>((size_t)(N + tk::kTile) * tk::kDim);
   t.qnorm = w.take<float>(Q);
-  t.scalars = w.take<int32_t>(2);
+  t.qerr = w.take<float>(Q);
+  t.scalars = w.take<int32_t>(4);
   t.unsafe = w.take<int32_t>(Q);
   t.cand_idx = w.take<int32_t>((size_t)nsplit * Q * kc);
   t.cand_score = w.take<float>((size_t)nsplit * Q * kc);
@@ -425,7 +518,8 @@ size_t tc_topk_workspace(int64_t Q, int64_t N, int k) {
   w.take<__nv_bfloat16>((size_t)(Q + tk::kRows) * tk::kDim);
   w.take<__nv_bfloat16>((size_t)(N + tk::kTile) * tk::kDim);
   w.take<float>(Q);
-  w.take<int32_t>(2);
+  w.take<float>(Q);
+  w.take<int32_t>(4);
   w.take<int32_t>(Q);
   w.take<int32_t>((size_t)nsplit * Q * kc);
   w.take<float>((size_t)nsplit * Q * kc);
@@ -433,7 +527,8 @@ size_t tc_topk_workspace(int64_t Q, int64_t N, int k) {
   return align_up(w.off, 1024) + 1024;
 }
 
-// Prepared bank image: bf16 rows [(N + kTile) x 128] followed (1024-byte aligned) by the bits of the largest row norm.
+// Prepared bank image: bf16 rows [(N + kTile) x 128] followed (1024-byte aligned) by the bits of max ||bf16(b)|| and of
+// max ||b - bf16(b)||.
 size_t tc_topk_bank_bytes(int64_t N) {
   return align_up((size_t)(N + tk::kTile) * tk::kDim * sizeof(__nv_bfloat16), 1024) + 1024;
 }
@@ -445,9 +540,9 @@ int tc_topk_prepare_bank(const float* bank, int64_t N, int D, void* prepared, si
                 tc_topk_bank_bytes(N));
   PCLIP_REQUIRE((reinterpret_cast<uintptr_t>(bank) & 15) == 0, PCLIP_ERR_INVALID, "topk: bank must be 16-byte aligned");
   int32_t* maxbits = reinterpret_cast<int32_t*>(static_cast<char*>(prepared) + tc_topk_bank_bytes(N) - 1024);
-  PCLIP_CHECK_CUDA(cudaMemsetAsync(maxbits, 0, sizeof(int32_t), st));
+  PCLIP_CHECK_CUDA(cudaMemsetAsync(maxbits, 0, 2 * sizeof(int32_t), st));
   to_bf16_norm_kernel<<<device_sm_count() * 8, 256, 0, st>>>(bank, N, static_cast<__nv_bfloat16*>(prepared), nullptr,
-                                                             maxbits);
+                                                             nullptr, maxbits);
   PCLIP_CHECK_LAUNCH();
   return PCLIP_OK;
 }
@@ -467,17 +562,17 @@ int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int 
   TopkWs t = carve(ws, ws_bytes, Q, N, k, kc, nsplit);
   PCLIP_REQUIRE(t.ok, PCLIP_ERR_WORKSPACE, "topk: workspace too small (%zu < %zu)", ws_bytes,
                 tc_topk_workspace(Q, N, k));
-  PCLIP_CHECK_CUDA(cudaMemsetAsync(t.scalars, 0, 2 * sizeof(int32_t), st));
+  PCLIP_CHECK_CUDA(cudaMemsetAsync(t.scalars, 0, 4 * sizeof(int32_t), st));
   const int cblocks = device_sm_count() * 8;
-  to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(q, Q, t.qb, t.qnorm, nullptr);
+  to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(q, Q, t.qb, t.qnorm, t.qerr, nullptr);
   PCLIP_CHECK_LAUNCH();
   const __nv_bfloat16* bb = t.bb;
   if (prepared) {   // persistent bf16 bank (pclip_topk_prepare_bank): no 3 N D-byte conversion pass per call
     bb = static_cast<const __nv_bfloat16*>(prepared);
     PCLIP_CHECK_CUDA(cudaMemcpyAsync(t.scalars, static_cast<const char*>(prepared) + tc_topk_bank_bytes(N) - 1024,
-                                     sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+                                     2 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   } else {
-    to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(bank, N, t.bb, nullptr, t.scalars);
+    to_bf16_norm_kernel<<<cblocks, 256, 0, st>>>(bank, N, t.bb, nullptr, nullptr, t.scalars);
     PCLIP_CHECK_LAUNCH();
   }
   CUtensorMap mq, mb;
@@ -489,14 +584,17 @@ int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int 
   dim3 grid((unsigned)ceil_div(Q, tk::kRows), (unsigned)nsplit);
   kern<<<grid, tk::kThreads, tk::kSmemBytes, st>>>(mq, mb, a);
   PCLIP_CHECK_LAUNCH();
-  topk_rescore_kernel<<<(unsigned)ceil_div(Q, kRescoreWarps), kRescoreWarps * 32, 0, st>>>(
-      q, bank, t.cand_idx, t.cand_score, t.qnorm, t.scalars, Q, nsplit, kc, k, index_base, idx, score, t.unsafe,
-      t.scalars + 1);
+  const int rw = rescore_warps(nsplit * kc);
+  const size_t rsmem = rw * rescore_warp_bytes(nsplit * kc);
+  PCLIP_CHECK_CUDA(cudaFuncSetAttribute(topk_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));
+  topk_rescore_kernel<<<(unsigned)ceil_div(Q, rw), rw * 32, rsmem, st>>>(
+      q, bank, t.cand_idx, t.cand_score, t.qnorm, t.qerr, t.scalars, Q, nsplit, kc, k, index_base, idx, score,
+      t.unsafe, t.scalars + 2);
   PCLIP_CHECK_LAUNCH();
   // queries whose exactness could not be proven are recomputed by the exact fp32 kernel (device-side count)
-  PCLIP_TRY(simt_topk(q, bank, Q, N, D, k, index_base, idx, score, t.fix, t.fix_bytes, st, t.unsafe, t.scalars + 1));
+  PCLIP_TRY(simt_topk(q, bank, Q, N, D, k, index_base, idx, score, t.fix, t.fix_bytes, st, t.unsafe, t.scalars + 2));
   if (n_unsafe)
-    PCLIP_CHECK_CUDA(cudaMemcpyAsync(n_unsafe, t.scalars + 1, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    PCLIP_CHECK_CUDA(cudaMemcpyAsync(n_unsafe, t.scalars + 2, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   return PCLIP_OK;
 }
 

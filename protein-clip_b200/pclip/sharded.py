@@ -107,13 +107,19 @@ class ShardedFilip:
         self.be = backend
         self.rs_native = dist.get_backend(group) == "nccl"       # gloo has no reduce-scatter: all-reduce + slice
 
-    def step(self, hA_l, hB_l, maskA_l, maskB_l, tau):
+    def step(self, hA_l, hB_l, maskA_l, maskB_l, tau, normalize: bool = False):
         """Local samples hA_l [Bl, TA, D], hB_l [Bl, TB, D], right-padded masks [Bl, T*]; tau 0-d.
-        Returns (global loss, dhA_l, dhB_l, dtau) -- the gradients of the GLOBAL mean loss."""
+        normalize=True applies ExtendedFILIP.forward's h / ||h|| (ref: modules/models.py:238-239) to the local shards
+        first -- what a training step does -- so that only NORMALISED B tokens travel and the gradients returned are
+        those of the raw tokens.  Returns (global loss, dhA_l, dhB_l, dtau): gradients of the GLOBAL mean loss."""
         g, P, r = self.group, self.P, self.rank
         Bl = hA_l.shape[0]
         B = Bl * P
-        hB_src, mB_src = hB_l.detach().contiguous(), maskB_l.contiguous()
+        hA = hA_l.detach().clone().requires_grad_(True)
+        hB_raw = hB_l.detach().clone().requires_grad_(normalize)
+        hA_in = self.be.normalize_scale(hA, None, eps=0.0) if normalize else hA
+        hB_n = self.be.normalize_scale(hB_raw, None, eps=0.0) if normalize else hB_raw
+        hB_src, mB_src = hB_n.detach().contiguous(), maskB_l.contiguous()
         if P > 1:
             hB_f = torch.empty((B,) + tuple(hB_src.shape[1:]), dtype=hB_src.dtype, device=hB_src.device)
             mB_f = torch.empty((B,) + tuple(mB_src.shape[1:]), dtype=mB_src.dtype, device=mB_src.device)
@@ -121,10 +127,9 @@ class ShardedFilip:
             dist.all_gather_into_tensor(mB_f, mB_src, group=g)
         else:
             hB_f, mB_f = hB_src.clone(), mB_src
-        hA = hA_l.detach().clone().requires_grad_(True)
         hB_f.requires_grad_(True)
         tau_l = torch.as_tensor(tau).detach().clone().to(hA.device).requires_grad_(True)
-        simA, simB = self.be.filip_similarity(hA, hB_f, maskA_l, mB_f, tau_l)
+        simA, simB = self.be.filip_similarity(hA_in, hB_f, maskA_l, mB_f, tau_l)
         # filip_loss is the mean over the LOCAL rows; Bl / B of it is this rank's share of the global mean
         loss = self.be.filip_loss(simA, simB, diag_offset=r * Bl) * (Bl / B)
         loss.backward()
@@ -141,6 +146,9 @@ class ShardedFilip:
                 dhB_l = dhB_f[r * Bl:(r + 1) * Bl].clone()
         else:
             dhB_l = dhB_f
+        if normalize:      # back through the local normalise of the B shard
+            hB_n.backward(dhB_l)
+            dhB_l = hB_raw.grad
         return loss_g, hA.grad, dhB_l, dtau
 
 
