@@ -156,6 +156,19 @@ int pclip_clip_loss(const pclip_chunk_t* x_chunks /* HOST */, int32_t nx, const 
                     float* dx /* [B, D] fp32 or NULL */, float* dy, void* workspace, size_t workspace_bytes,
                     pclip_stream_t stream);
 
+/* Small-batch CLIP step in ONE launch (B <= pclip_clip_small_max_batch(), D == 128; fp32 arithmetic): loss and -- when
+ * dx_chunks / dy_chunks are given -- the gradient of every leaf, multiplied by 1/(2B) and by *gscale (GradScaler's
+ * scale, ref: modules/training_utils.py:139; NULL = 1), written straight into the caller's per-leaf fp32 buffers
+ * (chunk i of dx has the rows of chunk i of x, col_stride 1).  This is the GradCache configuration
+ * (ref: modules/training_utils.py:247-265 on 16 + 16 leaves of [16, 128]): no torch.cat, no pack, no logits in HBM. */
+int32_t pclip_clip_small_max_batch(void);
+size_t pclip_clip_small_workspace_bytes(int64_t B);
+int pclip_clip_small_fused(const pclip_chunk_t* x_chunks /* HOST */, int32_t nx, const pclip_chunk_t* y_chunks /* HOST */,
+                           int32_t ny, int32_t in_dtype, int64_t B, int32_t D, const float* gscale /* dev [1] or NULL */,
+                           float* loss /* [1] */, const pclip_chunk_t* dx_chunks /* HOST, or NULL */,
+                           const pclip_chunk_t* dy_chunks /* HOST, or NULL */, void* workspace, size_t workspace_bytes,
+                           pclip_stream_t stream);
+
 /* out[i] = in[i] * (*g)   -- applies autograd's scalar grad_output on the device, no host sync */
 int pclip_scale_by_scalar(const float* in, const float* g /* dev [1] */, int64_t n, float* out,
                           pclip_stream_t stream);

@@ -2,7 +2,7 @@
 
 Restated from the published algorithm (Gao et al. 2021, "Scaling Deep Contrastive Learning Batch Size under
 Memory Limited Setup"); upstream source is not available offline, so this boundary is "parity unpinned" against
-upstream -- tests/test_gradcache.py pins it against the non-cached computation instead.  Call sites in the
+upstream -- tests/test_interface.py (test_grad_cache_shim_equals_direct_backward) pins it against the non-cached computation instead.  Call sites in the
 reference: modules/training_utils.py:126-127 (cached forward), :141-144 (closure replay), :157/:247 (cat).
 """
 from __future__ import annotations

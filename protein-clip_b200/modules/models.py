@@ -45,8 +45,24 @@ class _Trunk(nn.Module):
     def _build_ffn(self, embedding_dim, depth, dropout_rate):
         return _ffn(embedding_dim, depth, dropout_rate)
 
+    def _esm_is_replayable(self):
+        """True when a second forward of the ESM trunk on the same tokens must give the same hidden states and no
+        gradient flows into it: every parameter frozen (ref: main.py:22-23) and no active dropout inside it."""
+        esm = self.esm_model
+        if any(p.requires_grad for p in esm.parameters()):
+            return False
+        return not (esm.training and any(isinstance(m, nn.Dropout) and m.p > 0 for m in esm.modules()))
+
     def _residues(self, seq):
-        hidden = self.esm_model(input_ids=seq["input_ids"], attention_mask=seq["attention_mask"]).last_hidden_state
+        # GradCache runs every sub-batch twice (no-grad forward, then the closure's replay with grad, ref:
+        # modules/training_utils.py:126-144).  With a frozen trunk the replay's ESM forward recomputes exactly what the
+        # first one produced: train_gc asks (seq["_cache_esm"]) for the hidden states to be parked in the caller's dict,
+        # and the replay -- which receives the same dict -- picks them up instead of running 30 transformer layers again.
+        hidden = seq.get("_esm_hidden") if hasattr(seq, "get") else None
+        if hidden is None:
+            hidden = self.esm_model(input_ids=seq["input_ids"], attention_mask=seq["attention_mask"]).last_hidden_state
+            if hasattr(seq, "get") and seq.get("_cache_esm") and self._esm_is_replayable():
+                seq["_esm_hidden"] = hidden.detach()
         return self.amino_acid_ffn(self.projection(hidden))
 
 

@@ -10,8 +10,13 @@ What changed underneath:
     the same pass and scaled by autograd's grad_output (GradScaler's 65536) on the device.
   * under CUDA autocast (the GradCache path decorates its loss with autocast(), ref :247-249) the contraction runs on
     the bf16 tensor-core path, otherwise in fp32 -- the same split the reference gets from autocast's op lists.
-  * `eval_gc_allrec_onepep` keeps its loop protocol and return value but computes the rank with the rank kernel
-    instead of materialising a 256 x 256 matrix of identical rows to read its diagonal.
+  * `train_gc`: the frozen ESM trunk runs ONCE per sub-batch (its hidden states are parked in the
+    sub-batch's dict and reused by GradCache's replay), and the big-batch loss + the gradients of all 32 leaves come
+    from ONE kernel launch (pclip.ops.clip_loss_gc_direct) scaled by GradScaler's device-side scale.
+  * rank evaluation: `build_bank` encodes every sequence once, `rank_all` ranks ALL pairs with one
+    rank-kernel call, `topk_accuracy` is topk.py:53-61's cumulative histogram; `eval_gc_allrec_onepep` keeps its
+    signature and return value as a thin wrapper over the cached ranks (the reference re-encodes the whole candidate
+    set for each of its 256 calls, topk.py:47-51).
 """
 from __future__ import annotations
 
@@ -125,6 +130,7 @@ def train_gc(model, data_loader, tokenizer, optimizer, scaler, device, accumulat
         xx = _encode(tokenizer, pep_strings, device)
         yy = _encode(tokenizer, rec_strings, device)
         xx["temperature"] = yy["temperature"] = model.temperature
+        xx["_cache_esm"] = yy["_cache_esm"] = True      # frozen trunk: the replay reuses the hidden states
         rx, cx = _call_model_gc(model.pep_encoder, xx)
         ry, cy = _call_model_gc(model.rec_encoder, yy)
         acc.add(rx, cx, ry, cy)
@@ -132,10 +138,12 @@ def train_gc(model, data_loader, tokenizer, optimizer, scaler, device, accumulat
             continue
         groups += 1
         print(step)
-        loss = _contrastive_loss_gc(acc.reps_x, acc.reps_y)
+        # loss = _contrastive_loss_gc(cache_x, cache_y); scaler.scale(loss).backward() (ref :137-139) as one launch:
+        # the leaves' .grad are d(scale * loss) / d(rep), the scale being GradScaler's device tensor (no sync)
+        gscale = scaler.scale(torch.ones((), dtype=torch.float32, device=rx.device))
+        loss = ops.clip_loss_gc_direct(acc.reps_x, acc.reps_y, gscale)
         loss_sum += loss.item()
-        scaler.scale(loss).backward()      # leaves now hold d(scale * loss) / d(rep)
-        acc.replay()                       # second forward of each sub-batch, with grad, seeded by the leaf grads
+        acc.replay()                       # second pass of each sub-batch (head only), seeded by the leaf grads
         acc.reset()
         scaler.step(optimizer)
         scaler.update()
@@ -143,28 +151,70 @@ def train_gc(model, data_loader, tokenizer, optimizer, scaler, device, accumulat
     return loss_sum / groups
 
 
+# ---------------------------------------------------------------------------------------------------------
+# rank / top-k evaluation over an embedding bank built once (ref: :174-228, topk.py:47-61)
+# ---------------------------------------------------------------------------------------------------------
+def build_bank(model, data_loader, tokenizer, device, agg_batches=None):
+    """Encode every peptide and every receptor of the loader's first `agg_batches` sub-batches (None: all) ONCE, the
+    way the evaluation path encodes them (no grad, autocast as in _call_model_gc).  Returns (queries [N, D],
+    bank [N, D]) fp32: row i of the queries is the peptide whose positive is row i of the bank."""
+    model.eval()
+    qs, bs = [], []
+    with torch.no_grad():
+        for step, (pep_strings, rec_strings) in enumerate(data_loader):
+            if agg_batches is not None and step >= agg_batches:
+                break
+            xx = _encode(tokenizer, pep_strings, device)
+            yy = _encode(tokenizer, rec_strings, device)
+            xx["temperature"] = yy["temperature"] = model.temperature
+            with torch.autocast("cuda", enabled=torch.cuda.is_available()):
+                qs.append(model.pep_encoder(xx).float())
+                bs.append(model.rec_encoder(yy).float())
+    return torch.cat(qs, 0), torch.cat(bs, 0)
+
+
+def rank_all(model, data_loader, device, tokenizer, agg_batches=2):
+    """rank[k] = 1 + #{j : <pep_k, rec_j> > <pep_k, rec_k>} for EVERY pair k of the first `agg_batches` sub-batches
+    (strict compare, ref :219-222; exp is monotone, so ranking the dot products is ranking exp(logits)): one bank
+    build + ONE rank-kernel call instead of one pass over the loader per query.  int32 tensor [N] on the device."""
+    q, bank = build_bank(model, data_loader, tokenizer, device, agg_batches)
+    pos = torch.arange(q.shape[0], dtype=torch.int64, device=q.device)
+    return ops.rank_of_positive(q, bank, pos)
+
+
+def topk_accuracy(ranks, n=None):
+    """topk.py:53-61: histogram of the ranks, cumulative sum, divided by the number of candidates: accs[k] is the share
+    of queries whose positive ranks k or better (accs[0] is always 0: ranks start at 1).  A rank equal to the number of
+    candidates falls off the end of the reference's list (IndexError there); here it is simply never counted."""
+    ranks = torch.as_tensor(ranks).to(torch.int64).flatten().cpu()
+    n = int(n if n is not None else ranks.numel())
+    hist = torch.bincount(ranks.clamp(max=n), minlength=n + 1)[:n]
+    return (torch.cumsum(hist, 0).double() / n).tolist()
+
+
+_rank_cache = {}
+
+
+def _weights_version(model):
+    return sum(p._version for p in model.parameters())
+
+
 def eval_gc_allrec_onepep(model, data_loader, device, tokenizer, agg_batches=2, k=0):
     """Rank of the k-th pair's receptor among the first `agg_batches` sub-batches of receptors for the k-th peptide
-    (1 + number of candidates scoring strictly higher).  Returns [rank] after the first group, as the reference does."""
-    model.eval()
-    query = None
-    for i, (pep_strings, rec_strings) in enumerate(data_loader):
-        if k // len(pep_strings) == i:
-            query = pep_strings[k % len(rec_strings)]
-    bank, q_rep = [], None
-    for step, (pep_strings, rec_strings) in enumerate(data_loader):
-        yy = _encode(tokenizer, rec_strings, device)
-        yy["temperature"] = model.temperature
-        if q_rep is None:  # the reference re-encodes the same query for every candidate row; once is enough
-            xx = _encode(tokenizer, (query,), device)
-            xx["temperature"] = model.temperature
-            q_rep, _ = _call_model_gc(model.pep_encoder, xx)
-        ry, _ = _call_model_gc(model.rec_encoder, yy)
-        bank.append(ry.detach())
-        if (step + 1) % agg_batches == 0:
-            cand = torch.cat(bank, 0).float()
-            if not 0 <= k < cand.shape[0]:
-                raise IndexError(f"pair {k} is not among the first {cand.shape[0]} candidates")
-            pos = torch.tensor([k], dtype=torch.int64, device=cand.device)
-            rank = ops.rank_of_positive(q_rep.detach().float()[:1], cand, pos)
-            return [int(rank.item())]
+    (1 + number of candidates scoring strictly higher).  Returns [rank] after the first group, as the reference does.
+
+    The reference encodes the whole candidate set again on every call (32 ESM forwards per query, topk.py:47-51 makes
+    256 calls).  Here the first call for a (model weights, loader, agg_batches) encodes everything once and ranks every
+    pair with one kernel call; later calls are a lookup.  The cache is dropped when a parameter of the model changes
+    (in-place update counter) or another loader / model is passed."""
+    key = (id(model), id(data_loader), int(agg_batches), str(device))
+    ent = _rank_cache.get(key)
+    ver = _weights_version(model)
+    if ent is None or ent[0] != ver:
+        _rank_cache.clear()
+        ranks = rank_all(model, data_loader, device, tokenizer, agg_batches).cpu()
+        ent = _rank_cache[key] = (ver, ranks)
+    ranks = ent[1]
+    if not 0 <= k < ranks.numel():
+        raise IndexError(f"pair {k} is not among the first {ranks.numel()} candidates")
+    return [int(ranks[k])]

@@ -61,6 +61,10 @@ SIGNATURES = {
     "pclip_clip_workspace_bytes": (_SZ, [_I64, _I32, _I32]),
     "pclip_clip_loss": (C.c_int, [C.POINTER(Chunk), _I32, C.POINTER(Chunk), _I32, _I32, _I64, _I32, _I32, _P, _P, _P,
                                   _P, _P, _P, _SZ, _P]),
+    "pclip_clip_small_max_batch": (_I32, []),
+    "pclip_clip_small_workspace_bytes": (_SZ, [_I64]),
+    "pclip_clip_small_fused": (C.c_int, [C.POINTER(Chunk), _I32, C.POINTER(Chunk), _I32, _I32, _I64, _I32, _P, _P,
+                                         C.POINTER(Chunk), C.POINTER(Chunk), _P, _SZ, _P]),
     "pclip_scale_by_scalar": (C.c_int, [_P, _P, _I64, _P, _P]),
     "pclip_scores": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, _P, _P, _P]),
     "pclip_rank_workspace_bytes": (_SZ, [_I64]),

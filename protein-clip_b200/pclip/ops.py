@@ -109,6 +109,12 @@ def clip_loss_raw(xs, ys, compute: int, want_grad: bool, want_lse: bool = False)
     if sum(t.shape[0] for t in ys) != B or any(t.shape[1] != D for t in xs + ys):
         raise L.PclipError("clip_loss: x and y must hold the same number of [*, D] rows")
     lib = L.lib()
+    if not want_lse and _small_fused_ok(B, D, len(xs), len(ys)):
+        # small batch (the GradCache configuration): ONE cooperative launch instead of pack / sum-exp / finalize / grad
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        dxy = torch.empty(2, B, D, dtype=torch.float32, device=dev) if want_grad else None
+        _small_fused(xs, ys, B, D, None, loss, dxy)
+        return loss, (dxy[0] if want_grad else None), (dxy[1] if want_grad else None), None, None
     with torch.cuda.device(dev):     # the workspace plan depends on the SM count of the tensors' device
         nbytes = lib.pclip_clip_workspace_bytes(B, D, compute)
     owner, ws = L.workspace(nbytes, dev)
@@ -124,6 +130,75 @@ def clip_loss_raw(xs, ys, compute: int, want_grad: bool, want_lse: bool = False)
                                     L.stream_ptr(dev)))
     owner.record_stream(torch.cuda.current_stream(dev))
     return loss, dx, dy, rl, cl
+
+
+def _small_fused_ok(B: int, D: int, nx: int, ny: int) -> bool:
+    return (D == 128 and B <= int(L.lib().pclip_clip_small_max_batch()) and nx <= MAX_CHUNKS and ny <= MAX_CHUNKS
+            and os.environ.get("PCLIP_SMALL_FUSED", "1") != "0")
+
+
+_small_ws = {}      # device -> (owner, aligned pointer, bytes): the fused kernel's 3 B floats of scratch, stream-ordered
+
+
+def _small_workspace(dev, B):
+    ent = _small_ws.get(dev)
+    need = int(L.lib().pclip_clip_small_workspace_bytes(int(L.lib().pclip_clip_small_max_batch())))
+    if ent is None:
+        owner, p = L.workspace(need, dev)
+        ent = _small_ws[dev] = (owner, p, need)
+    return ent[1], ent[2]
+
+
+def _out_chunks(buf_ptr: int, row_counts, D: int):
+    """Chunk descriptors of consecutive row blocks of one contiguous fp32 [sum(rows), D] buffer (no tensor objects)."""
+    import struct
+    flat, r = [], 0
+    for n in row_counts:
+        flat += (buf_ptr + r * D * 4, n, D, 1)
+        r += n
+    return (L.Chunk * len(row_counts)).from_buffer_copy(struct.pack(f"{len(flat)}q", *flat))
+
+
+def _small_fused(xs, ys, B, D, gscale, loss, grad_buf):
+    """pclip_clip_small_fused on row chunks xs / ys.  grad_buf: contiguous fp32 [2 B, D] (rows of x, then rows of y)
+    that receives the gradients chunk by chunk, or None for the loss only.  Kernels on one stream run in order, so the
+    scratch is one persistent buffer per device."""
+    lib = L.lib()
+    dev = xs[0].device
+    with torch.cuda.device(dev):
+        ws, nbytes = _small_workspace(dev, B)
+        gx = gy = None
+        if grad_buf is not None:
+            base = grad_buf.data_ptr()
+            gx = _out_chunks(base, [t.shape[0] for t in xs], D)
+            gy = _out_chunks(base + B * D * 4, [t.shape[0] for t in ys], D)
+        L.check(lib.pclip_clip_small_fused(L.chunks_of(xs), len(xs), L.chunks_of(ys), len(ys), L.dtype_code(xs[0].dtype),
+                                           B, D, L.ptr(gscale), L.ptr(loss), gx, gy, ws, nbytes, L.stream_ptr(dev)))
+
+
+def clip_loss_gc_direct(xs, ys, gscale: torch.Tensor | None = None) -> torch.Tensor:
+    """GradCache fast path (ref: modules/training_utils.py:137-139: loss = _contrastive_loss_gc(cache_x, cache_y);
+    scaler.scale(loss).backward()): ONE kernel launch computes the loss and writes d(gscale * loss) / d(leaf) into the
+    `.grad` of every leaf -- no autograd graph over the 32 leaves, no host sync (gscale is GradScaler's device-side
+    scale).  Falls back to the autograd path when the batch does not fit the fused kernel.  Returns the (unscaled) loss."""
+    xs, ys = list(xs), list(ys)
+    L.require_cuda(*xs, *ys)
+    B, D = sum(t.shape[0] for t in xs), xs[0].shape[1]
+    same = all(t.dtype == xs[0].dtype for t in xs + ys) and xs[0].dtype in (torch.float32, torch.bfloat16)
+    if not (same and sum(t.shape[0] for t in ys) == B and _small_fused_ok(B, D, len(xs), len(ys))):
+        loss = clip_loss(xs, ys, compute=BF16 if D == 128 else F32)
+        (loss if gscale is None else loss * gscale.reshape(())).backward()
+        return loss.detach()
+    dev = xs[0].device
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    buf = torch.empty(2 * B, D, dtype=torch.float32, device=dev)
+    gs = None if gscale is None else gscale.detach().reshape(1).float()
+    _small_fused(xs, ys, B, D, gs, loss, buf)
+    for leaf, g in zip(xs + ys, buf.split([t.shape[0] for t in xs + ys])):
+        if leaf.requires_grad:
+            g = g if leaf.dtype == torch.float32 else g.to(leaf.dtype)
+            leaf.grad = g if leaf.grad is None else leaf.grad + g
+    return loss.reshape(())
 
 
 class _ClipInfoNCE(torch.autograd.Function):

@@ -98,13 +98,14 @@ class ShardedFilip:
     samples of it; the loss and d tau are all-reduced scalars.  Token length TB must be padded to the same value on all
     ranks.  `backend` (default pclip.ops) supplies `filip_similarity` and `filip_loss`; tests inject the oracle."""
 
-    def __init__(self, group=None, backend=None):
+    def __init__(self, group=None, backend=None, compute=None):
         self.group = group
         self.P = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         if backend is None:
             from . import ops as backend
         self.be = backend
+        self.kw = {} if compute is None else {"compute": compute}     # pclip.ops.F32 / BF16 (default: PCLIP_COMPUTE)
         self.rs_native = dist.get_backend(group) == "nccl"       # gloo has no reduce-scatter: all-reduce + slice
 
     def step(self, hA_l, hB_l, maskA_l, maskB_l, tau, normalize: bool = False):
@@ -129,7 +130,7 @@ class ShardedFilip:
             hB_f, mB_f = hB_src.clone(), mB_src
         hB_f.requires_grad_(True)
         tau_l = torch.as_tensor(tau).detach().clone().to(hA.device).requires_grad_(True)
-        simA, simB = self.be.filip_similarity(hA_in, hB_f, maskA_l, mB_f, tau_l)
+        simA, simB = self.be.filip_similarity(hA_in, hB_f, maskA_l, mB_f, tau_l, **self.kw)
         # filip_loss is the mean over the LOCAL rows; Bl / B of it is this rank's share of the global mean
         loss = self.be.filip_loss(simA, simB, diag_offset=r * Bl) * (Bl / B)
         loss.backward()

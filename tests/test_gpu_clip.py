@@ -46,7 +46,11 @@ def test_library_loads_and_counts_launches(ops):
     ops.reset_launch_count()
     x = torch.randn(16, 128, device="cuda")
     ops.clip_loss(x, x)
-    assert ops.launch_count() >= 3
+    assert ops.launch_count() == 1          # B <= 512: the one-launch small-batch kernel
+    ops.reset_launch_count()
+    big = torch.randn(1024, 128, device="cuda") / 11.3
+    ops.clip_loss(big, big, compute=ops.BF16)
+    assert ops.launch_count() >= 3         # pack, sum-exp, finalize (no gradient wanted)
 
 
 def test_encoder_tail(ops, golden):
@@ -233,3 +237,44 @@ def test_gradcache_more_than_32_leaves(ops):
     assert_close(loss, lo, 1e-5, "loss, 40 leaves")
     assert_close(torch.cat([t.grad for t in xs]), dxo, 3e-5, "dx, 40 leaves")
     assert_close(torch.cat([t.grad for t in ys]), dyo, 3e-5, "dy, 40 leaves")
+
+
+@pytest.mark.parametrize("name", ["clip_b16", "clip_b37", "clip_b256"])
+def test_small_fused_kernel_against_reference_golden(ops, golden, name):
+    """The one-launch small-batch kernel (pclip_clip_small_fused: fp32 arithmetic, cooperative grid barrier) against
+    the reference's own loss and gradients, to the fp32 tolerance -- through autograd and through the launch counter."""
+    g = golden(name)
+    pep, rec = g["pep"].cuda().requires_grad_(), g["rec"].cuda().requires_grad_()
+    ops.reset_launch_count()
+    loss = ops.clip_loss(pep, rec.t().t(), compute=ops.BF16)     # B <= 512: the fused kernel serves both compute modes
+    assert ops.launch_count() == 1
+    loss.backward()
+    assert_close(loss, g["loss"], 1e-5, "loss")
+    assert_close(pep.grad, g["dpep"], 3e-5, "dpep")
+    assert_close(rec.grad, g["drec"], 3e-5, "drec")
+
+
+def test_gradcache_direct_path(ops, golden):
+    """train_gc's loss step (ref: modules/training_utils.py:137-139) as ONE launch: 16 + 16 leaves, GradScaler's
+    device-side scale 65536, gradients written straight into the leaves' .grad; against the reference's golden."""
+    g = golden("clip_gradcache_16x16")
+    xs = [t.cuda().requires_grad_() for t in g["x"]]
+    ys = [t.cuda().requires_grad_() for t in g["y"]]
+    scale = torch.tensor(65536.0, device="cuda")
+    ops.reset_launch_count()
+    loss = ops.clip_loss_gc_direct(xs, ys, scale)
+    assert ops.launch_count() == 1 and loss.grad_fn is None
+    assert_close(loss, g["loss"], 1e-5, "loss")
+    assert_close(torch.stack([t.grad for t in xs]), g["dx"], 3e-5, "leaf grads x")
+    assert_close(torch.stack([t.grad for t in ys]), g["dy"], 3e-5, "leaf grads y")
+    # a second group accumulates into existing .grad like autograd would
+    loss2 = ops.clip_loss_gc_direct(xs, ys, scale)
+    assert_close(torch.stack([t.grad for t in xs]), 2 * g["dx"], 3e-5, "accumulated")
+    # ragged leaves, bf16 leaves and a batch too large for the fused kernel take the same entry point
+    x, y = torch.randn(600, 128).cuda(), torch.randn(600, 128).cuda()
+    x, y = x / x.norm(dim=-1, keepdim=True), y / y.norm(dim=-1, keepdim=True)
+    big = [t.requires_grad_() for t in (x[:100].clone(), x[100:].clone())], [y.clone().requires_grad_()]
+    lb = ops.clip_loss_gc_direct(big[0], big[1])
+    lo, dxo, dyo, _, _ = R.clip_loss_and_grads(R.bf16_round(x.cpu()).double(), R.bf16_round(y.cpu()).double())
+    assert_close(lb, lo, 1e-2, "fallback loss")
+    assert_close(torch.cat([t.grad for t in big[0]]), dxo, 1e-2, "fallback grads")

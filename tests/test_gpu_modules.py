@@ -147,3 +147,85 @@ def test_filip_process_batch_matches_oracle():
     assert abs(tf.evaluate(model, [batch], tok, DEV) - float(lo_val)) <= 1e-5 * abs(float(lo_val))
     assert float(tf._contrastive_loss(rA.detach(), use_dcl=True)) == pytest.approx(
         float(R.filip_contrastive_loss(rA.detach().cpu(), use_dcl=True)), rel=1e-5)
+
+
+def test_train_gc_fp32_trunk_to_1e2(clip_model, monkeypatch):
+    """with the trunk in fp32 (autocast switched off for this test) what is left between train_gc
+    and the un-cached 32-pair batch is the GradCache plumbing -- ESM hidden states cached across the replay, one-launch
+    loss + leaf gradients scaled by GradScaler's device scale -- and the loss kernel: 1e-2 (bf16 bar) on every
+    parameter gradient, in fact ~1e-5 because the small-batch kernel computes in fp32."""
+    import contextlib
+    from modules import training_utils as tu
+    monkeypatch.setattr(tu.torch, "autocast", lambda *a, **k: contextlib.nullcontext())
+    tok = _tiny.TinyTokenizer()
+    data = _tiny.loader(4, 8, seed=5)
+    model = clip_model
+    ref = copy.deepcopy(model)
+    opt = torch.optim.SGD([p for p in model.parameters() if p.requires_grad], lr=0.0)
+    scaler = torch.amp.GradScaler("cuda", init_scale=65536.0)
+    grads = {}
+    orig_step = scaler.step
+
+    def spy(optimizer):
+        for n, p in model.named_parameters():
+            if p.grad is not None:
+                grads[n] = p.grad.detach().clone() / 65536.0
+        return orig_step(optimizer)
+
+    scaler.step = spy
+    calls = {"n": 0}
+    esm = model.pep_encoder.esm_model
+    orig_fwd = esm.forward
+
+    def counting(*a, **k):
+        calls["n"] += 1
+        return orig_fwd(*a, **k)
+
+    esm.forward = counting
+    loss = tu.train_gc(model, data, tok, opt, scaler, DEV, accumulated_batches=4)
+    esm.forward = orig_fwd
+    assert calls["n"] == 8, "frozen ESM trunk must run once per sub-batch and modality (4 x 2), not twice"
+    reps_x = [_oracle_encoder(ref.pep_encoder, tok(b[0]).to(DEV), ref.temperature) for b in data]
+    reps_y = [_oracle_encoder(ref.rec_encoder, tok(b[1]).to(DEV), ref.temperature) for b in data]
+    lo = R.clip_loss_gc(reps_x, reps_y)
+    lo.backward()
+    assert abs(loss - float(lo)) <= 1e-5 * abs(float(lo))
+    n_checked = 0
+    for n, q in ref.named_parameters():
+        if q.grad is not None and q.grad.abs().max() > 0:
+            assert n in grads and rel(grads[n], q.grad) <= 1e-2, (n, rel(grads[n], q.grad))
+            n_checked += 1
+    assert n_checked >= 10
+
+
+def test_rank_all_equals_per_query_protocol(clip_model):
+    """one bank build + ONE rank-kernel call gives the ranks of all 32 pairs; they equal what the
+    reference's protocol (one eval_gc_allrec_onepep call per k, topk.py:47-51) returns, and topk_accuracy reproduces
+    topk.py:53-61's cumulative histogram."""
+    from modules import training_utils as tu
+    from pclip import ops
+    tok = _tiny.TinyTokenizer()
+    data = _tiny.loader(4, 8, seed=9)
+    model = clip_model.eval()
+    ops.reset_launch_count()
+    ranks = tu.rank_all(model, data, DEV, tok, agg_batches=4)
+    assert ops.launch_count() <= 2 + 16        # 2 rank kernels + the 8 x 2 encoder-tail normalisations of the bank build
+    assert ranks.shape == (32,)
+    with torch.no_grad():
+        reps_y = torch.cat([_oracle_encoder(model.rec_encoder, tok(b[1]).to(DEV), model.temperature) for b in data])
+        want = []
+        for k in range(32):
+            q = _oracle_encoder(model.pep_encoder, tok((data[k // 8][0][k % 8],)).to(DEV), model.temperature)
+            want.append(R.rank_of_positive((q @ reps_y.t()).exp()[0].cpu(), k))
+    assert ranks.cpu().tolist() == want
+    tu._rank_cache.clear()
+    per_call = [tu.eval_gc_allrec_onepep(model, data, DEV, tok, agg_batches=4, k=k)[0] for k in range(32)]
+    assert per_call == want
+    ok = [r for r in want if r < 32]
+    assert tu.topk_accuracy(ok, 32) == pytest.approx(R.topk_accuracy_from_ranks(ok, 32))
+    # a parameter update invalidates the cached ranks
+    with torch.no_grad():
+        model.rec_encoder.projection.weight.add_(0.5 * torch.randn_like(model.rec_encoder.projection.weight))
+    assert len(tu._rank_cache) == 1
+    tu.eval_gc_allrec_onepep(model, data, DEV, tok, agg_batches=4, k=0)
+    assert next(iter(tu._rank_cache.values()))[0] == tu._weights_version(model)

@@ -11,8 +11,9 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("mode", ["f32", "bf16"])
 @pytest.mark.parametrize("P,B", [(2, 512), (4, 1024), (8, 2048), (4, 4096)])
-def test_emulated_ranks_match_single_gpu(P, B, mode):
+def test_emulated_ranks_match_single_gpu(P, B, mode, monkeypatch):
     from pclip import ops, synth
+    monkeypatch.setenv("PCLIP_SMALL_FUSED", "0")   # the single-GPU reference must run the SAME (large-batch) kernels
     compute = ops.F32 if mode == "f32" else ops.BF16
     x, y = synth.clip_scaled_embeddings(B, 128, cfg_id=40 + P, trained_like=True)
     xd, yd = x.cuda(), y.cuda()
