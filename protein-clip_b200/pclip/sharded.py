@@ -87,6 +87,33 @@ class ShardedClip:
         rec("grad", 0); s.grad(self.B, gscale); rec("grad", 1)
         return s.loss, s.dx, s.dy
 
+    # -----------------------------------------------------------------------------------------------------
+    # CUDA-graph replay.  At 8 GPUs one step is ~0.8 ms of which the two tensor-core kernels are 0.64: the rest is two
+    # NCCL launches and ~20 small kernels whose HOST launch cost (about 5 us each through Python + ctypes) leaves the GPU
+    # idle between them.  All buffers of a step are owned by the plan, so the whole step -- pack, both collectives,
+    # forward sweep, finalize, gradient -- is captured once and replayed with one launch.
+    # -----------------------------------------------------------------------------------------------------
+    def capture(self, xs, ys, gscale=None):
+        """Capture step(xs, ys) into a CUDA graph.  xs / ys (and gscale) must be the tensors every later replay reads
+        (fill them in place before replay()).  Returns self."""
+        dev = self.s.dev
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):            # warm-up outside the capture: NCCL channel set-up, lazy workspaces
+            for _ in range(3):
+                self.step(xs, ys, gscale)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._out = self.step(xs, ys, gscale)
+        return self
+
+    def replay(self):
+        """One launch for the whole step captured by capture(); returns (loss [1], dX_local, dY_local)."""
+        self._graph.replay()
+        return self._out
+
 
 class ShardedFilip:
     """FILIP token-wise loss with the A-batch rows sharded over the ranks (configs[2]).
