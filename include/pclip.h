@@ -71,10 +71,13 @@ void pclip_launch_count_reset(void);
 int pclip_normalize_scale_fwd(const float* e, int64_t rows, int32_t D, const float* tau /* dev [1] or NULL */,
                               float eps, float* out /* [rows, D] */, float* inv_norm /* [rows] saved */,
                               pclip_stream_t stream);
-/* de = (s / n) * (g - nhat * <g, nhat>),  dtau += 0.5 * sum(g * out)   (dtau may be NULL) */
+/* scratch of the grid-wide sums below (dtau, row-wise loss): summed in a fixed order, so results are reproducible
+ * run to run (no float atomics) */
+size_t pclip_rowsum_workspace_bytes(int64_t rows);
+/* de = (s / n) * (g - nhat * <g, nhat>),  dtau += 0.5 * sum(g * out)   (dtau may be NULL: then no workspace is needed) */
 int pclip_normalize_scale_bwd(const float* grad_out, const float* out, const float* inv_norm, int64_t rows,
                               int32_t D, const float* tau, float* de, float* dtau /* dev [1], accumulated */,
-                              pclip_stream_t stream);
+                              void* workspace, size_t workspace_bytes, pclip_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * (2) CLIP InfoNCE, symmetric cross entropy over S = X Y^T.
@@ -252,6 +255,7 @@ int pclip_filip_bwd(const float* hA, const float* hB, const int32_t* lenA, const
  * ref: modules/training_utils_filip.py:15-23 */
 int pclip_rowwise_infonce(const float* logits, int64_t B, int64_t Bc, int64_t diag_offset, float scale,
                           float* loss /* [1], accumulated */, float* dlogits /* [B,Bc] or NULL */,
+                          void* workspace /* pclip_rowsum_workspace_bytes(B) */, size_t workspace_bytes,
                           pclip_stream_t stream);
 
 #ifdef __cplusplus

@@ -53,6 +53,7 @@ struct Args {
   float* rowsum;         // [2][B] workspace: sum_j exp(s_ij) per row of each side
   float* diag;           // [B]    workspace: s_ii
   int want_grad;
+  int vec;               // every leaf is fp32, row-major (col stride 1), 16-byte aligned rows: float4 staging
 };
 
 __device__ __forceinline__ float load_elem(const Side& s, int chunk, int row_in_chunk, int d, int in_bf16) {
@@ -84,6 +85,23 @@ __device__ __forceinline__ void stage_rows(const Side& s, int r0, int nrows, int
     *reinterpret_cast<float4*>(dst + r * kLd + lane * 4) = v;
   }
 }
+// Vector path: the 64 rows of a tile are 16 independent float4 loads per thread, issued together (and, in the loops
+// below, one tile ahead of the arithmetic): a row-by-row staging loop paid one global-memory latency per row and made
+// the kernel 110 us long at B = 256 (profiles/r02_clip_small_fused_kernel_ncu_full.txt: 5 % issue utilisation).
+__device__ __forceinline__ void load_tile(const float* const* rowp, int j0, int B, float4 (&pre)[kTile / 4]) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int it = 0; it < kTile / 4; ++it) {
+    const int row = j0 + it * 4 + warp;
+    pre[it] = row < B ? __ldg(reinterpret_cast<const float4*>(rowp[row]) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+__device__ __forceinline__ void store_tile(const float4 (&pre)[kTile / 4], float* b_s) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int it = 0; it < kTile / 4; ++it) *reinterpret_cast<float4*>(b_s + (it * 4 + warp) * kLd + lane * 4) = pre[it];
+}
 }  // namespace cs
 
 __global__ void __launch_bounds__(cs::kThreads) clip_small_fused_kernel(const __grid_constant__ cs::Args args) {
@@ -95,6 +113,7 @@ __global__ void __launch_bounds__(cs::kThreads) clip_small_fused_kernel(const __
   float* b_s = a_s + kStrip * kLd;          // [kTile][kLd]    staged rows of the other modality
   float* e_s = b_s + kTile * kLd;           // [kStrip][Bpad]  exp(s), later g
   float* red = e_s + kStrip * Bpad;         // [kStrip][16]    row-sum partials
+  const float** rowp = reinterpret_cast<const float**>(red + kStrip * 16);   // [B] row starts of the other modality
   const int strips = (B + kStrip - 1) / kStrip;
   const int sd = blockIdx.x / strips;       // 0: rows of x against y, 1: rows of y against x
   const int r0 = (blockIdx.x - sd * strips) * kStrip;
@@ -103,12 +122,23 @@ __global__ void __launch_bounds__(cs::kThreads) clip_small_fused_kernel(const __
   const int tid = threadIdx.x;
   const int r = tid >> 4, cgp = tid & 15;   // phase A: row r of the strip, columns cgp + 16 k of the staged tile
 
+  const bool vec = args.vec != 0;
+  if (vec) {
+    for (int row = tid; row < B; row += kThreads) {
+      const int k = find_chunk(Bo, row);
+      rowp[row] = static_cast<const float*>(Bo.in[k]) + (int64_t)(row - Bo.row_begin[k]) * Bo.in_rs[k];
+    }
+  }
   stage_rows(A, r0, kStrip, B, args.in_bf16, a_s);
+  __syncthreads();
+  float4 pre[kTile / 4];
+  if (vec) load_tile(rowp, 0, B, pre);
   float rsum = 0.f;
   for (int j0 = 0; j0 < B; j0 += kTile) {
-    __syncthreads();                        // previous tile consumed (and a_s visible on the first pass)
-    stage_rows(Bo, j0, kTile, B, args.in_bf16, b_s);
+    __syncthreads();                        // previous tile consumed
+    if (vec) store_tile(pre, b_s); else stage_rows(Bo, j0, kTile, B, args.in_bf16, b_s);
     __syncthreads();
+    if (vec && j0 + kTile < B) load_tile(rowp, j0 + kTile, B, pre);      // in flight under this tile's arithmetic
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 8
     for (int d = 0; d < kDim; d += 4) {
@@ -168,10 +198,12 @@ __global__ void __launch_bounds__(cs::kThreads) clip_small_fused_kernel(const __
   // dA[r, :] = sum_j g[r, j] b_j: thread = (row r, dims dq*4 .. +3 and 64 + dq*4 .. +3)
   const int dq = tid & 15;
   float4 d0 = make_float4(0.f, 0.f, 0.f, 0.f), d1 = d0;
+  if (vec) load_tile(rowp, 0, B, pre);
   for (int j0 = 0; j0 < B; j0 += kTile) {
     __syncthreads();
-    stage_rows(Bo, j0, kTile, B, args.in_bf16, b_s);
+    if (vec) store_tile(pre, b_s); else stage_rows(Bo, j0, kTile, B, args.in_bf16, b_s);
     __syncthreads();
+    if (vec && j0 + kTile < B) load_tile(rowp, j0 + kTile, B, pre);
 #pragma unroll 8
     for (int j = 0; j < kTile; ++j) {
       const float g = e_s[r * Bpad + j0 + j];
@@ -255,10 +287,15 @@ int pclip_clip_small_fused(const pclip_chunk_t* x_chunks, int32_t nx, const pcli
   a.rowsum = static_cast<float*>(workspace);
   a.diag = a.rowsum + 2 * B;
   a.want_grad = dx_chunks != nullptr;
+  a.vec = in_dtype == PCLIP_F32;
+  for (int sd = 0; sd < 2 && a.vec; ++sd)
+    for (int i = 0; i < a.side[sd].n; ++i)
+      if (a.side[sd].in_cs[i] != 1 || (a.side[sd].in_rs[i] & 3) != 0 || (reinterpret_cast<uintptr_t>(a.side[sd].in[i]) & 15) != 0)
+        a.vec = 0;
   const int strips = (int)ceil_div(B, cs::kStrip);
   const int Bpad = (int)ceil_div(B, cs::kTile) * cs::kTile + 4;
   const size_t smem = sizeof(float) * ((size_t)cs::kStrip * cs::kLd + (size_t)cs::kTile * cs::kLd +
-                                       (size_t)cs::kStrip * Bpad + cs::kStrip * 16);
+                                       (size_t)cs::kStrip * Bpad + cs::kStrip * 16) + sizeof(void*) * (size_t)B + 16;
   PCLIP_CHECK_CUDA(cudaFuncSetAttribute(clip_small_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   PCLIP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, clip_small_fused_kernel, cs::kThreads, smem));

@@ -161,11 +161,33 @@ __global__ void normalize_fwd_kernel(const float* __restrict__ e, int64_t rows, 
   if (lane == 0 && inv_norm) inv_norm[row] = (nrm > eps || eps == 0.f) ? inv : -inv;  // sign flags the clamped case
 }
 
+// Grid-wide sum with a FIXED summation order (run-to-run reproducible, unlike float atomicAdd): every block parks its
+// partial, the block that takes the last ticket adds all partials in index order.  `scratch` = [gridDim.x] floats followed
+// by one ticket counter that the host zeroes before the launch (atomicInc wraps it back to 0).  v is read from thread 0.
+__device__ __forceinline__ void ordered_grid_sum(float v, float* scratch, float scale, float* out) {
+  __shared__ bool last;
+  unsigned* ticket = reinterpret_cast<unsigned*>(scratch + gridDim.x);
+  if (threadIdx.x == 0) {
+    scratch[blockIdx.x] = v;
+    __threadfence();
+    last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (last && threadIdx.x < 32) {
+    __threadfence();
+    float s = 0.f;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += 32) s += *reinterpret_cast<volatile float*>(scratch + i);
+    s = warp_sum(s);
+    if (threadIdx.x == 0) *out += s * scale;
+  }
+}
+
 // de = (s * inv) * (g - nhat <g, nhat>)  (projection dropped when the norm was clamped to eps);
 // dtau += 0.5 * sum(g * out)
 __global__ void normalize_bwd_kernel(const float* __restrict__ g, const float* __restrict__ out,
                                      const float* __restrict__ inv_norm, int64_t rows, int D,
-                                     const float* __restrict__ tau, float* __restrict__ de, float* __restrict__ dtau) {
+                                     const float* __restrict__ tau, float* __restrict__ de, float* __restrict__ dtau,
+                                     float* __restrict__ scratch) {
   const int lane = threadIdx.x & 31;
   const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   float go = 0.f;
@@ -188,11 +210,12 @@ __global__ void normalize_bwd_kernel(const float* __restrict__ g, const float* _
     const int w = threadIdx.x >> 5;
     if (lane == 0) red[w] = row < rows ? go : 0.f;
     __syncthreads();
+    float v = 0.f;
     if (w == 0) {
-      float v = lane < (int)(blockDim.x >> 5) ? red[lane] : 0.f;
+      v = lane < (int)(blockDim.x >> 5) ? red[lane] : 0.f;
       v = warp_sum(v);
-      if (lane == 0) atomicAdd(dtau, 0.5f * v);
     }
+    ordered_grid_sum(v, scratch, 0.5f, dtau);
   }
 }
 
@@ -283,7 +306,8 @@ __global__ void scale_by_scalar_kernel(const float* __restrict__ in, const float
 // (max-subtracted LSE: equal to the reference's naive exp wherever that is finite)
 // ---------------------------------------------------------------------------------------------
 __global__ void rowwise_infonce_kernel(const float* __restrict__ logits, int64_t B, int64_t Bc, int64_t diag_offset,
-                                       float scale, float* __restrict__ loss, float* __restrict__ dlogits) {
+                                       float scale, float* __restrict__ loss, float* __restrict__ dlogits,
+                                       float* __restrict__ scratch) {
   const int lane = threadIdx.x & 31;
   const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   float term = 0.f;
@@ -308,11 +332,12 @@ __global__ void rowwise_infonce_kernel(const float* __restrict__ logits, int64_t
   const int w = threadIdx.x >> 5;
   if (lane == 0) red[w] = row < B ? term : 0.f;
   __syncthreads();
+  float v = 0.f;
   if (w == 0) {
-    float v = lane < (int)(blockDim.x >> 5) ? red[lane] : 0.f;
+    v = lane < (int)(blockDim.x >> 5) ? red[lane] : 0.f;
     v = warp_sum(v);
-    if (lane == 0) atomicAdd(loss, v * scale);
   }
+  ordered_grid_sum(v, scratch, scale, loss);
 }
 
 }  // namespace pclip
@@ -350,15 +375,31 @@ int pclip_normalize_scale_fwd(const float* e, int64_t rows, int32_t D, const flo
   return PCLIP_OK;
 }
 
+// scratch of the ordered grid sums: one float per block of 8 rows + the ticket counter
+size_t pclip_rowsum_workspace_bytes(int64_t rows) { return align_up((size_t)(ceil_div(rows, 8) + 1) * sizeof(float), 1024); }
+
+static int zero_ticket(void* workspace, size_t workspace_bytes, int64_t rows, cudaStream_t st, float** scratch) {
+  PCLIP_REQUIRE(workspace && (reinterpret_cast<uintptr_t>(workspace) & 1023) == 0 &&
+                    workspace_bytes >= pclip_rowsum_workspace_bytes(rows),
+                PCLIP_ERR_WORKSPACE, "workspace missing, misaligned or too small (pclip_rowsum_workspace_bytes)");
+  *scratch = static_cast<float*>(workspace);
+  PCLIP_CHECK_CUDA(cudaMemsetAsync(*scratch + ceil_div(rows, 8), 0, sizeof(unsigned), st));
+  return PCLIP_OK;
+}
+
 int pclip_normalize_scale_bwd(const float* grad_out, const float* out, const float* inv_norm, int64_t rows, int32_t D,
-                              const float* tau, float* de, float* dtau, pclip_stream_t stream) {
+                              const float* tau, float* de, float* dtau, void* workspace, size_t workspace_bytes,
+                              pclip_stream_t stream) {
   PCLIP_TRY(require_device());
   PCLIP_REQUIRE(grad_out && out && inv_norm && de && rows >= 0 && D > 0, PCLIP_ERR_INVALID,
                 "normalize_bwd: bad argument");
   if (rows == 0) return PCLIP_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* scratch = nullptr;
+  if (dtau) PCLIP_TRY(zero_ticket(workspace, workspace_bytes, rows, st, &scratch));
   const int threads = 256;
-  normalize_bwd_kernel<<<(unsigned)ceil_div(rows * 32, threads), threads, 0, static_cast<cudaStream_t>(stream)>>>(
-      grad_out, out, inv_norm, rows, D, tau, de, dtau);
+  normalize_bwd_kernel<<<(unsigned)ceil_div(rows * 32, threads), threads, 0, st>>>(grad_out, out, inv_norm, rows, D, tau,
+                                                                                  de, dtau, scratch);
   PCLIP_CHECK_LAUNCH();
   return PCLIP_OK;
 }
@@ -390,13 +431,16 @@ int pclip_scale_by_scalar(const float* in, const float* g, int64_t n, float* out
 }
 
 int pclip_rowwise_infonce(const float* logits, int64_t B, int64_t Bc, int64_t diag_offset, float scale, float* loss,
-                          float* dlogits, pclip_stream_t stream) {
+                          float* dlogits, void* workspace, size_t workspace_bytes, pclip_stream_t stream) {
   PCLIP_TRY(require_device());
   PCLIP_REQUIRE(logits && loss && B > 0 && Bc > 0 && diag_offset >= 0 && diag_offset + B <= Bc, PCLIP_ERR_INVALID,
                 "rowwise_infonce: bad argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* scratch = nullptr;
+  PCLIP_TRY(zero_ticket(workspace, workspace_bytes, B, st, &scratch));
   const int threads = 256;
-  rowwise_infonce_kernel<<<(unsigned)ceil_div(B * 32, threads), threads, 0, static_cast<cudaStream_t>(stream)>>>(
-      logits, B, Bc, diag_offset, scale, loss, dlogits);
+  rowwise_infonce_kernel<<<(unsigned)ceil_div(B * 32, threads), threads, 0, st>>>(logits, B, Bc, diag_offset, scale, loss,
+                                                                                dlogits, scratch);
   PCLIP_CHECK_LAUNCH();
   return PCLIP_OK;
 }

@@ -142,7 +142,7 @@ __global__ void filip_dtau_kernel(const float* __restrict__ gA, const float* __r
     float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (threadIdx.x == 0) atomicAdd(dtau, -v / tau[0]);
+    if (threadIdx.x == 0) dtau[0] += -v / tau[0];   // single block: a fixed summation order, no atomics
   }
 }
 

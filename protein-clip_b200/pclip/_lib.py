@@ -48,7 +48,8 @@ SIGNATURES = {
     "pclip_launch_count": (_I64, []),
     "pclip_launch_count_reset": (None, []),
     "pclip_normalize_scale_fwd": (C.c_int, [_P, _I64, _I32, _P, _F, _P, _P, _P]),
-    "pclip_normalize_scale_bwd": (C.c_int, [_P, _P, _P, _I64, _I32, _P, _P, _P, _P]),
+    "pclip_rowsum_workspace_bytes": (_SZ, [_I64]),
+    "pclip_normalize_scale_bwd": (C.c_int, [_P, _P, _P, _I64, _I32, _P, _P, _P, _P, _SZ, _P]),
     "pclip_pack": (C.c_int, [C.POINTER(Chunk), _I32, _I32, _I64, _I32, _I32, _P, _P, _I64, _P]),
     "pclip_transpose_bf16": (C.c_int, [_P, _I64, _I32, _P, _I64, _P]),
     "pclip_clip_rowsumexp_workspace_bytes": (_SZ, [_I64, _I64, _I32, _I32]),
@@ -79,7 +80,7 @@ SIGNATURES = {
     "pclip_filip_fwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _I32, _P, _P, _P, _P, _P, _SZ, _P]),
     "pclip_filip_bwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P,
                                   _P, _P, _SZ, _P]),
-    "pclip_rowwise_infonce": (C.c_int, [_P, _I64, _I64, _I64, _F, _P, _P, _P]),
+    "pclip_rowwise_infonce": (C.c_int, [_P, _I64, _I64, _I64, _F, _P, _P, _P, _SZ, _P]),
 }
 
 _lib = None

@@ -60,9 +60,13 @@ class _NormalizeScale(torch.autograd.Function):
         de = torch.empty_like(out)
         dtau = torch.zeros(1, dtype=torch.float32, device=out.device) if ctx.has_tau else None
         with torch.cuda.device(out.device):
+            nbytes = int(L.lib().pclip_rowsum_workspace_bytes(rows)) if ctx.has_tau else 0
+            owner, ws = L.workspace(nbytes, out.device) if ctx.has_tau else (None, None)
             L.check(L.lib().pclip_normalize_scale_bwd(L.ptr(g2), L.ptr(out), L.ptr(inv), rows, D,
                                                       L.ptr(tau_d) if ctx.has_tau else None, L.ptr(de), L.ptr(dtau),
-                                                      L.stream_ptr(out.device)))
+                                                      ws, nbytes, L.stream_ptr(out.device)))
+        if owner is not None:
+            owner.record_stream(torch.cuda.current_stream(out.device))
         return de.reshape(ctx.shape), (dtau.reshape(ctx.tau_shape) if ctx.has_tau else None), None
 
 
@@ -629,8 +633,11 @@ class _RowwiseInfoNCE(torch.autograd.Function):
         loss = torch.zeros(1, dtype=torch.float32, device=lg.device)
         dl = torch.empty_like(lg) if logits.requires_grad else None
         with torch.cuda.device(lg.device):
+            nbytes = int(L.lib().pclip_rowsum_workspace_bytes(B))
+            owner, ws = L.workspace(nbytes, lg.device)
             L.check(L.lib().pclip_rowwise_infonce(L.ptr(lg), B, Bc, diag_offset, float(weight) / B, L.ptr(loss), L.ptr(dl),
-                                                  L.stream_ptr(lg.device)))
+                                                  ws, nbytes, L.stream_ptr(lg.device)))
+        owner.record_stream(torch.cuda.current_stream(lg.device))
         if dl is not None:
             ctx.save_for_backward(dl)
         ctx.in_dtype = logits.dtype
