@@ -118,8 +118,8 @@ def _fasta_parse(path, fmt="fasta"):
 
 def install_stubs():
     try:
-        import Bio  # noqa: F401
-    except Exception:
+        from Bio import PDB, SeqIO  # noqa: F401
+    except Exception:  # absent, or a partial stub another test left in sys.modules
         bio = _module("Bio")
         bio.SeqIO = _module("Bio.SeqIO", parse=_fasta_parse)
         pdb = _Anything("Bio.PDB")

@@ -23,7 +23,7 @@ def _run(script, tmp_path, pairs=400):
     torch.set_num_threads(min(8, os.cpu_count() or 1))
     err = H.run_script(script, str(tmp_path), backend="oracle" if not torch.cuda.is_available() else "cuda", pairs=pairs)
     runs = glob.glob(str(tmp_path / "runs" / "*"))
-    assert len(runs) == 1
+    assert len(runs) == 1, getattr(err, "harness_traceback", err)
     return err, runs[0]
 
 
