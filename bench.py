@@ -276,7 +276,9 @@ class ClipLarge:
 
     def config(self):
         return {"workload": self.name, "B": self.B, "D": self.D, "compute": "bf16 tcgen05, fp32 accumulate",
-                "sharding": f"rows/{self.dist.world} + all-gather" if self.dist.on else "single GPU",
+                "sharding": (f"rows/{self.dist.world}; Y all-gather (NCCL) in front of the forward sweep, X "
+                             + ("pulled from peer memory by the copy engines under it" if self.job.pull is not None
+                                else "in the same NCCL launch")) if self.dist.on else "single GPU",
                 "l2": "no flush: per-step working set ~300 MB (fp32 in 67, bf16 packed 34, fp32 grads 67, column-sum "
                       "partials 134) > 126 MB L2"}
 

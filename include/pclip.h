@@ -131,6 +131,13 @@ int pclip_clip_finalize(const float* rowsum, const float* colsum, const float* d
                         float* row_lse, float* col_lse, float* rinv, float* cinv, float* loss /* [1] */,
                         pclip_stream_t stream);
 
+/* Row-sharded job, after the all-gather of every rank's forward record
+ * stats_all [P][Nb + 2 Ma] = [colsum partial (Nb) | rowsum (Ma) | diag (Ma)]: column sums added in rank order, R and S_ii
+ * laid out by global row (diag_full [Nb]), then the same per-row terms and loss as pclip_clip_finalize over all Nb rows. */
+int pclip_clip_finalize_sharded(const float* stats_all, int32_t P, int64_t Nb, int64_t Ma, float scale, float* row_lse,
+                                float* col_lse, float* rinv, float* cinv, float* diag_full, float* loss /* [1] */,
+                                pclip_stream_t stream);
+
 typedef struct {
   const void* a;     /* [Ma, D] */
   const void* b;     /* [Nb, D] */

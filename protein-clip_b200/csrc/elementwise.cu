@@ -267,6 +267,27 @@ __global__ void __launch_bounds__(1024) clip_loss_sum_kernel(const float* __rest
   }
 }
 
+// Row shard, after the all-gather of every rank's record [C partial (Nb) | R (Ma) | S_ii (Ma)]: reduce the column
+// partials in rank order, lay R and S_ii out by global row and finalise all Nb rows -- one launch instead of a
+// reduction, two strided copies and the per-row kernel.
+__global__ void clip_finalize_sharded_kernel(const float* __restrict__ stats, int P, int64_t Nb, int64_t Ma,
+                                             float* __restrict__ row_lse, float* __restrict__ col_lse,
+                                             float* __restrict__ rinv, float* __restrict__ cinv,
+                                             float* __restrict__ diag_full) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= Nb) return;
+  const int64_t rec = Nb + 2 * Ma;
+  float c = 0.f;
+  for (int p = 0; p < P; ++p) c += stats[p * rec + j];
+  const int64_t p = j / Ma, i = j - p * Ma;
+  const float r = stats[p * rec + Nb + i];
+  row_lse[j] = logf(r);
+  col_lse[j] = logf(c);
+  rinv[j] = 1.0f / r;
+  cinv[j] = 1.0f / c;
+  diag_full[j] = stats[p * rec + Nb + Ma + i];
+}
+
 // single-block variant for callers that do not want the log-sums stored
 __global__ void __launch_bounds__(1024) clip_finalize_kernel(const float* __restrict__ rowsum, const float* __restrict__ colsum,
                                      const float* __restrict__ diag, int64_t M, float scale,
@@ -416,6 +437,23 @@ int pclip_clip_finalize(const float* rowsum, const float* colsum, const float* d
   } else {
     clip_finalize_kernel<<<1, 1024, 0, st>>>(rowsum, colsum, diag, M, scale, row_lse, col_lse, rinv, cinv, loss);
   }
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+int pclip_clip_finalize_sharded(const float* stats_all, int32_t P, int64_t Nb, int64_t Ma, float scale, float* row_lse,
+                                float* col_lse, float* rinv, float* cinv, float* diag_full, float* loss,
+                                pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(stats_all && row_lse && col_lse && rinv && cinv && diag_full && loss, PCLIP_ERR_INVALID,
+                "finalize_sharded: null argument");
+  PCLIP_REQUIRE(P >= 1 && Ma > 0 && Nb == (int64_t)P * Ma, PCLIP_ERR_INVALID,
+                "finalize_sharded: Nb must be P * Ma (got P=%d Ma=%lld Nb=%lld)", P, (long long)Ma, (long long)Nb);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  clip_finalize_sharded_kernel<<<(unsigned)ceil_div(Nb, 256), 256, 0, st>>>(stats_all, P, Nb, Ma, row_lse, col_lse, rinv,
+                                                                           cinv, diag_full);
+  PCLIP_CHECK_LAUNCH();
+  clip_loss_sum_kernel<<<1, 1024, 0, st>>>(row_lse, col_lse, diag_full, Nb, scale, loss);
   PCLIP_CHECK_LAUNCH();
   return PCLIP_OK;
 }

@@ -57,6 +57,7 @@ SIGNATURES = {
     "pclip_clip_sumexp_workspace_bytes": (_SZ, [_I64, _I64, _I32, _I32]),
     "pclip_clip_sumexp": (C.c_int, [_P, _P, _I64, _I64, _I64, _I32, _I32, _P, _P, _P, _P, _SZ, _P]),
     "pclip_clip_finalize": (C.c_int, [_P, _P, _P, _I64, _F, _P, _P, _P, _P, _P, _P]),
+    "pclip_clip_finalize_sharded": (C.c_int, [_P, _I32, _I64, _I64, _F, _P, _P, _P, _P, _P, _P, _P]),
     "pclip_clip_grad_workspace_bytes": (_SZ, [_I64, _I64, _I32, _I32]),
     "pclip_clip_grad": (C.c_int, [C.POINTER(BwdSide), _I32, _I32, _I32, _F, _P, _P, _SZ, _P]),
     "pclip_clip_workspace_bytes": (_SZ, [_I64, _I32, _I32]),

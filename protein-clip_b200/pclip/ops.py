@@ -295,7 +295,7 @@ class ClipPlan:
             self.colsum_f = self.stats_l[:Nb]
             self.rowsum = self.stats_l[Nb:Nb + Ma]
             self.diag = self.stats_l[Nb + Ma:]
-            self.rowsum_full, self.colsum_full, self.diag_full = (torch.empty(Nb, **f32) for _ in range(3))
+            self.diag_full = torch.empty(Nb, **f32)
             self.row_lse_f, self.col_lse_f = torch.empty(Nb, **f32), torch.empty(Nb, **f32)
             self.rinv = self.rinv_f[diag_offset:diag_offset + Ma]
             self.cinv = self.cinv_f[diag_offset:diag_offset + Ma]
@@ -369,14 +369,10 @@ class ClipPlan:
         """Row shard, after the all-gather of every rank's [C partial | R | S_ii] record (`stats_all` [P, Nb + 2 Ma]):
         reduce the column partials, lay R and S_ii out by global row, and finalise ALL rows here -- the loss comes out
         global on every rank and 1/R, 1/C of every row are local, so no further exchange is needed."""
-        Nb, Ma = self.Nb, self.Ma
-        P = stats_all.shape[0]
-        torch.sum(stats_all[:, :Nb], dim=0, out=self.colsum_full)
-        self.rowsum_full.view(P, Ma).copy_(stats_all[:, Nb:Nb + Ma])
-        self.diag_full.view(P, Ma).copy_(stats_all[:, Nb + Ma:])
-        L.check(L.lib().pclip_clip_finalize(L.ptr(self.rowsum_full), L.ptr(self.colsum_full), L.ptr(self.diag_full), Nb,
-                                            0.5 / B_total, L.ptr(self.row_lse_f), L.ptr(self.col_lse_f),
-                                            L.ptr(self.rinv_f), L.ptr(self.cinv_f), L.ptr(self.loss), self._st()))
+        L.check(L.lib().pclip_clip_finalize_sharded(L.ptr(stats_all), stats_all.shape[0], self.Nb, self.Ma,
+                                                    0.5 / B_total, L.ptr(self.row_lse_f), L.ptr(self.col_lse_f),
+                                                    L.ptr(self.rinv_f), L.ptr(self.cinv_f), L.ptr(self.diag_full),
+                                                    L.ptr(self.loss), self._st()))
 
     @_on_device
     def grad(self, B_total: int, gscale: torch.Tensor | None = None):

@@ -23,8 +23,55 @@ backend; the product constructs ClipPlan and nothing else.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
+
+
+class _PeerRows:
+    """This rank's packed X shard in symmetric memory (torch.distributed._symmetric_memory: every rank maps every peer's
+    buffer into its own address space), and the copy-engine all-gather built on it: P plain device-to-device copies on a
+    side stream that read the peers' shards over NVLink while the SMs run the forward sweep.  An NCCL all-gather in that
+    position was measured and lost (its kernel takes SMs away from a whole-wave grid); copy engines take none."""
+
+    def __init__(self, like: torch.Tensor, group):
+        import torch.distributed._symmetric_memory as symm
+        grp = group if group is not None else dist.group.WORLD
+        self.P, self.rank = dist.get_world_size(grp), dist.get_rank(grp)
+        self.local = symm.empty(tuple(like.shape), dtype=like.dtype, device=like.device)
+        self.hdl = symm.rendezvous(self.local, grp)
+        self.peers = [self.local if p == self.rank else self.hdl.get_buffer(p, tuple(like.shape), like.dtype)
+                      for p in range(self.P)]
+        self.stream = torch.cuda.Stream(like.device)
+
+    @staticmethod
+    def create(like, group):
+        """None unless symmetric memory comes up on EVERY rank (the decision is all-reduced: a rank pulling from a peer
+        that kept its shard in private memory would read garbage)."""
+        try:
+            pr = _PeerRows(like, group)
+            ok = 1
+        except Exception:
+            pr, ok = None, 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=like.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        return pr if int(flag.item()) == 1 else None
+
+    def start(self, full: torch.Tensor):
+        """Enqueue the gather of all shards into `full` [P * Ma, D] on the side stream, ordered after everything the
+        current stream has enqueued so far.  The caller guarantees that every peer's shard is complete by then (here:
+        the NCCL all-gather of Y that precedes it was entered by every peer after its pack)."""
+        main = torch.cuda.current_stream(full.device)
+        self.stream.wait_stream(main)
+        Ma = self.local.shape[0]
+        with torch.cuda.stream(self.stream):
+            for k in range(1, self.P + 1):                      # ring order: no two ranks start on the same peer
+                p = (self.rank + k) % self.P
+                full[p * Ma:(p + 1) * Ma].copy_(self.peers[p], non_blocking=True)
+
+    def join(self, dev):
+        torch.cuda.current_stream(dev).wait_stream(self.stream)
 
 
 class ShardedClip:
@@ -45,6 +92,13 @@ class ShardedClip:
             self.stats_all = torch.empty(self.P, stages.stats_l.numel(), dtype=stages.stats_l.dtype,
                                          device=stages.stats_l.device)
         self.coalesce = self.P > 1 and dist.get_backend(group) == "nccl"
+        # X is not needed before the gradient: pull it over the copy engines under the forward sweep (PCLIP_PEER_PULL=0
+        # keeps both gathers on NCCL in front of the sweep)
+        self.pull = None
+        if self.fused and self.coalesce and os.environ.get("PCLIP_PEER_PULL", "1") != "0":
+            self.pull = _PeerRows.create(stages.xl, group)
+            if self.pull is not None:
+                stages.xl = self.pull.local
 
     def step(self, xs, ys, gscale=None, events=None):
         """xs / ys: this rank's row chunks.  Returns (global loss [1], dX_local [Ma, D], dY_local [Ma, D])."""
@@ -55,9 +109,17 @@ class ShardedClip:
                 events[name][i].record(torch.cuda.current_stream(s.dev))
 
         s.pack(xs, ys)
-        if self.P > 1:
-            # (Tried: gather Y first and let X travel under the forward sweep.  The NCCL kernel then holds SMs the
-            # whole-wave grid of the sweep counts on: sweep 222 -> 262 us, two gathers 2 x 52 us instead of 75 us.)
+        if self.pull is not None:
+            # Y by NCCL: the sweep needs it, and its completion here means every peer has packed (stream order on the
+            # peer: pack X, pack Y, all-gather).  X then travels on the copy engines under the sweep.  Re-use of the shard
+            # buffer by the next step is safe: a peer cannot leave this step's record all-gather before this rank has
+            # entered it, which is after the join below.
+            dist.all_gather_into_tensor(s.yf, s.yl, group=g)
+            self.pull.start(s.xf)
+        elif self.P > 1:
+            # (Tried: gather Y first and let X travel under the forward sweep AS A SECOND NCCL GATHER.  The NCCL kernel
+            # then holds SMs the whole-wave grid of the sweep counts on: sweep 222 -> 262 us, two gathers 2 x 52 us
+            # instead of 75 us.)
             if self.coalesce:
                 with dist._coalescing_manager(group=g):      # one ncclGroup: a single launch for both gathers
                     dist.all_gather_into_tensor(s.xf, s.xl, group=g)
@@ -68,6 +130,8 @@ class ShardedClip:
         s.transpose_full()
         if self.fused:
             rec("rowsumexp", 0); s.sumexp(); rec("rowsumexp", 1)
+            if self.pull is not None:
+                self.pull.join(s.dev)
             dist.all_gather_into_tensor(self.stats_all.view(-1), s.stats_l, group=g)
             s.finalize_full(self.stats_all, self.B)
         else:
