@@ -98,6 +98,11 @@ int pclip_normalize_scale_bwd(const float* grad_out, const float* out, const flo
  * outT [D, ldT] (ldT >= rows, multiple of 64; needed by the bf16 gradient kernel).  NULL = not wanted. */
 int pclip_pack(const pclip_chunk_t* chunks /* HOST */, int32_t n, int32_t in_dtype, int64_t rows, int32_t D,
                int32_t out_dtype, void* out, void* outT, int64_t ldT, pclip_stream_t stream);
+/* both modalities of a step (two chunk lists of the same total shape) with ONE launch, no transposed copies
+ * (ref: the torch.cat of GradCache's two leaf lists, modules/training_utils.py:247-249) */
+int pclip_pack_pair(const pclip_chunk_t* x_chunks /* HOST */, int32_t nx, const pclip_chunk_t* y_chunks /* HOST */,
+                    int32_t ny, int32_t in_dtype, int64_t rows, int32_t D, int32_t out_dtype, void* out_x, void* out_y,
+                    pclip_stream_t stream);
 /* outT[d, r] = in[r, d] for packed bf16 [rows, D] (used after an all-gather) */
 int pclip_transpose_bf16(const void* in, int64_t rows, int32_t D, void* outT, int64_t ldT, pclip_stream_t stream);
 
@@ -133,10 +138,12 @@ int pclip_clip_finalize(const float* rowsum, const float* colsum, const float* d
 
 /* Row-sharded job, after the all-gather of every rank's forward record
  * stats_all [P][Nb + 2 Ma] = [colsum partial (Nb) | rowsum (Ma) | diag (Ma)]: column sums added in rank order, R and S_ii
- * laid out by global row (diag_full [Nb]), then the same per-row terms and loss as pclip_clip_finalize over all Nb rows. */
+ * taken by global row, then the same per-row terms and loss as pclip_clip_finalize over all Nb rows, in ONE launch; the
+ * loss terms are added in a fixed order (bit-reproducible; P = 1 is the single-GPU case and gives the same bits). */
+size_t pclip_clip_finalize_sharded_workspace_bytes(int64_t Nb);
 int pclip_clip_finalize_sharded(const float* stats_all, int32_t P, int64_t Nb, int64_t Ma, float scale, float* row_lse,
-                                float* col_lse, float* rinv, float* cinv, float* diag_full, float* loss /* [1] */,
-                                pclip_stream_t stream);
+                                float* col_lse, float* rinv, float* cinv, float* loss /* [1] */, void* workspace,
+                                size_t workspace_bytes, pclip_stream_t stream);
 
 typedef struct {
   const void* a;     /* [Ma, D] */

@@ -33,15 +33,6 @@ int device_sm_count() {
   return cached_sms;
 }
 
-int clip_generation() {
-  static int gen = 0;
-  if (!gen) {
-    const char* e = getenv("PCLIP_CLIP_GEN");
-    gen = (e && e[0] == '1') ? 1 : 2;
-  }
-  return gen;
-}
-
 int require_device() {
   int n = 0;
   cudaError_t e = cudaGetDeviceCount(&n);
@@ -72,20 +63,19 @@ size_t pclip_clip_rowsumexp_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, i
 size_t pclip_clip_grad_workspace_bytes(int64_t Ma, int64_t Nb, int32_t D, int32_t compute) {
   (void)D;
   if (compute != PCLIP_COMPUTE_BF16) return 0;
-  return std::max(tc_grad_workspace(Ma, Nb), tc2_grad_workspace(Ma, Nb));
+  return tc2_grad_workspace(Ma, Nb);
 }
 
 static size_t ld_transposed(int64_t rows) { return align_up((size_t)rows, 64); }
 
 size_t pclip_clip_workspace_bytes(int64_t B, int32_t D, int32_t compute) {
-  // packed X, Y (+ transposed copies in bf16 mode), 6 per-row vectors, kernel scratch, alignment slack
+  // packed X, Y, 8 per-row vectors, kernel scratch, alignment slack
   const bool tc = compute == PCLIP_COMPUTE_BF16;
   const size_t esz = tc ? 2 : 4;
   size_t n = 2 * align_up((size_t)B * D * esz, 1024) + 8 * align_up((size_t)B * sizeof(float), 1024);
   if (tc) {
-    n += 2 * align_up((size_t)D * ld_transposed(B) * esz, 1024);
     const size_t a = std::max(tc_rowsumexp_workspace(B, B), tc2_sumexp_workspace(B, B));
-    const size_t b = std::max(tc_grad_workspace(B, B), tc2_grad_workspace(B, B));
+    const size_t b = tc2_grad_workspace(B, B);
     n += align_up(a > b ? a : b, 1024);
   }
   return n + 16 * 1024;
@@ -124,8 +114,7 @@ int pclip_clip_grad(const pclip_clip_bwd_side_t* sides, int32_t n_sides, int32_t
   PCLIP_REQUIRE(sides && n_sides >= 1 && n_sides <= 2, PCLIP_ERR_INVALID, "grad: n_sides must be 1 or 2");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (compute == PCLIP_COMPUTE_BF16)
-    return clip_generation() == 1 ? tc_grad(sides, n_sides, D, scale, gscale, workspace, workspace_bytes, st)
-                                  : tc2_grad(sides, n_sides, D, scale, gscale, workspace, workspace_bytes, st);
+    return tc2_grad(sides, n_sides, D, scale, gscale, workspace, workspace_bytes, st);
   if (compute == PCLIP_COMPUTE_F32) return simt_grad(sides, n_sides, D, scale, gscale, st);
   return fail(PCLIP_ERR_UNSUPPORTED, "grad: unknown compute mode %d", compute);
 }
@@ -156,13 +145,11 @@ int pclip_clip_loss(const pclip_chunk_t* x_chunks, int32_t nx, const pclip_chunk
   char* Y = ws.take<char>((size_t)B * D * esz);
   char* XT = nullptr;
   char* YT = nullptr;
-  if (tc && want_grad && clip_generation() == 1) {  // only the first-generation gradient kernel reads transposes
-    XT = ws.take<char>((size_t)D * ldT * esz);
-    YT = ws.take<char>((size_t)D * ldT * esz);
-  }
-  float* rowsum = ws.take<float>(B);
-  float* colsum = ws.take<float>(B);
-  float* diag = ws.take<float>(B);
+  // one record [C | R | S_ii], the layout pclip_clip_finalize_sharded reads (P = 1)
+  float* stats = ws.take<float>(3 * (size_t)B);
+  float* colsum = stats;
+  float* rowsum = stats + B;
+  float* diag = stats + 2 * B;
   float* diag2 = ws.take<float>(B);
   float* rinv = ws.take<float>(B);
   float* cinv = ws.take<float>(B);
@@ -176,14 +163,18 @@ int pclip_clip_loss(const pclip_chunk_t* x_chunks, int32_t nx, const pclip_chunk
   PCLIP_TRY(pack_operands(x_chunks, nx, y_chunks, ny, in_dtype, B, D, cdt, X, XT, Y, YT, ldT, st));
   // below 2048 columns the two-sided forward keeps the column sums fp32-exact (the single pass sums bf16-rounded
   // exps: the rounding averages out over thousands of rows, not over 16)
-  if (tc && clip_generation() != 1 && B >= 2048) {
+  if (tc && B >= 2048) {
     PCLIP_TRY(pclip_clip_sumexp(X, Y, B, B, 0, D, compute, rowsum, colsum, diag, scratch, scratch_bytes, stream));
   } else {
     pclip_clip_fwd_side_t f[2] = {{X, Y, B, B, 0, rowsum, diag}, {Y, X, B, B, 0, colsum, diag2}};
     PCLIP_TRY(pclip_clip_rowsumexp(f, 2, D, compute, scratch, scratch_bytes, stream));
   }
   const float scale = 0.5f / (float)B;
-  PCLIP_TRY(pclip_clip_finalize(rowsum, colsum, diag, B, scale, rl, cl, rinv, cinv, loss, stream));
+  if (B >= 4096 && scratch_bytes >= pclip_clip_finalize_sharded_workspace_bytes(B)) {
+    PCLIP_TRY(pclip_clip_finalize_sharded(stats, 1, B, B, scale, rl, cl, rinv, cinv, loss, scratch, scratch_bytes, stream));
+  } else {
+    PCLIP_TRY(pclip_clip_finalize(rowsum, colsum, diag, B, scale, rl, cl, rinv, cinv, loss, stream));
+  }
   if (want_grad) {
     pclip_clip_bwd_side_t g[2] = {{X, Y, YT, ldT, B, B, 0, rinv, cinv, dx}, {Y, X, XT, ldT, B, B, 0, cinv, rinv, dy}};
     PCLIP_TRY(pclip_clip_grad(g, 2, D, compute, scale, nullptr, scratch, scratch_bytes, stream));

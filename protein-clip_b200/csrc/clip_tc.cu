@@ -6,8 +6,8 @@
 // :260-264 (the same under autocast).  D is fixed at 128 (ref: main.py:27 embedding_dim).
 //
 //   tc_rowsumexp_kernel : rowsum_i = sum_j exp(a_i . b_j), diag_i = a_i . b_(off+i)
-//   tc_grad_kernel      : da_i = sum_j exp(a_i . b_j) (rinv_i + cinv_j) b_j      (P is re-quantised to bf16 and fed
-//                         back to the tensor core as the A operand of a second MMA whose B operand is b^T)
+//   (two-sided forward: the production path below 2048 columns, where its fp32-exact column sums matter; the
+//   single-pass forward and the gradient kernel live in clip_tc2.cu)
 //
 // All shared-memory operand tiles are K-major [128 rows x 64 bf16] panels (128 B per row, SWIZZLE_128B).
 #include <cuda_bf16.h>
@@ -264,332 +264,32 @@ int tc_rowsumexp(const pclip_clip_fwd_side_t* sides, int n_sides, int D, void* w
   return PCLIP_OK;
 }
 
-// =================================================================================================================
-// grad
-// =================================================================================================================
-struct TcBwdSide {
-  int64_t Ma, Nb, diag_offset;
-  const float* rinv;
-  const float* cinv;
-  const __nv_bfloat16* b;  // packed [Nb, 128] (for the -2 b_pos term)
-  float* out;              // nsplit == 1: da [Ma, 128];  else partial [nsplit][Ma][128]
-};
-struct TcBwdArgs {
-  TcBwdSide s[2];
-  int tiles_per_split;
-  int direct;  // 1: finish da in the kernel (nsplit == 1)
-  float scale;
-  const float* gscale;
-};
-
-constexpr int kBwdStages = 2;  // per ring (b and bT)
-// a | b ring | bT ring | P x2 | barriers | cinv staging
-constexpr uint32_t kBwdTiles = 1 + 2 * kBwdStages + 2;
-constexpr uint32_t kBwdSmemBytes = kTileBytes * kBwdTiles + 256 + 2 * kTile * 4 + 1024;
-
-__global__ void __launch_bounds__(kThreads, 1)
-tc_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__ CUtensorMap tb0,
-               const __grid_constant__ CUtensorMap tbt0, const __grid_constant__ CUtensorMap ta1,
-               const __grid_constant__ CUtensorMap tb1, const __grid_constant__ CUtensorMap tbt1,
-               const TcBwdArgs args) {
-  const TcBwdSide& sd = args.s[blockIdx.z];
-  const CUtensorMap* ta = blockIdx.z == 0 ? &ta0 : &ta1;
-  const CUtensorMap* tb = blockIdx.z == 0 ? &tb0 : &tb1;
-  const CUtensorMap* tbt = blockIdx.z == 0 ? &tbt0 : &tbt1;
-  const int64_t row0 = (int64_t)blockIdx.x * kTile;
-  if (row0 >= sd.Ma) return;
-  const int ntiles_all = (int)((sd.Nb + kTile - 1) / kTile);
-  const int tile_begin = blockIdx.y * args.tiles_per_split;
-  const int tile_end = min(tile_begin + args.tiles_per_split, ntiles_all);
-  const int ntiles = max(tile_end - tile_begin, 0);
-
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* a_tile = smem;
-  uint8_t* b_tiles = a_tile + kTileBytes;
-  uint8_t* bt_tiles = b_tiles + kBwdStages * kTileBytes;
-  uint8_t* p_tiles = bt_tiles + kBwdStages * kTileBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(p_tiles + 2 * kTileBytes);
-  uint64_t* a_full = bars;                      // 1
-  uint64_t* b_full = a_full + 1;                // kBwdStages
-  uint64_t* b_empty = b_full + kBwdStages;      // kBwdStages
-  uint64_t* bt_full = b_empty + kBwdStages;     // kBwdStages
-  uint64_t* bt_empty = bt_full + kBwdStages;    // kBwdStages
-  uint64_t* s_full = bt_empty + kBwdStages;     // 2
-  uint64_t* s_empty = s_full + 2;               // 2
-  uint64_t* p_full = s_empty + 2;               // 2
-  uint64_t* p_empty = p_full + 2;               // 2
-  uint64_t* da_full = p_empty + 2;              // 1
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(da_full + 1);
-  float* cinv_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);  // [2][128]
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-
-  if (threadIdx.x == 0) {
-    mbar_init(a_full, 1);
-    for (int i = 0; i < kBwdStages; ++i) {
-      mbar_init(&b_full[i], 1);
-      mbar_init(&b_empty[i], 1);
-      mbar_init(&bt_full[i], 1);
-      mbar_init(&bt_empty[i], 1);
-    }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&s_full[i], 1);
-      mbar_init(&s_empty[i], kEpiThreads);
-      mbar_init(&p_full[i], kEpiThreads);
-      mbar_init(&p_empty[i], 1);
-    }
-    mbar_init(da_full, 1);
-    fence_mbar_init();
-  }
-  if (warp == 1) tmem_alloc<512>(tmem_slot);
-  tc_fence_before_sync();
-  __syncthreads();
-  tc_fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_da = tmem_base + 2 * kTile;
-
-  if (warp == 0) {
-    if (lane == 0) {
-      tma_prefetch_desc(ta);
-      tma_prefetch_desc(tb);
-      tma_prefetch_desc(tbt);
-      mbar_arrive_expect_tx(a_full, kTileBytes);
-      tma_load_2d(a_tile, ta, a_full, 0, (int32_t)row0);
-      tma_load_2d(a_tile + kPanelBytes, ta, a_full, 64, (int32_t)row0);
-      for (int t = 0; t < ntiles; ++t) {
-        const int stage = t % kBwdStages;
-        const uint32_t phase = (uint32_t)(t / kBwdStages) & 1u;
-        const int32_t col0 = (tile_begin + t) * kTile;
-        mbar_wait(&b_empty[stage], phase ^ 1u);
-        mbar_arrive_expect_tx(&b_full[stage], kTileBytes);
-        uint8_t* dst = b_tiles + (size_t)stage * kTileBytes;
-        tma_load_2d(dst, tb, &b_full[stage], 0, col0);
-        tma_load_2d(dst + kPanelBytes, tb, &b_full[stage], 64, col0);
-        mbar_wait(&bt_empty[stage], phase ^ 1u);
-        mbar_arrive_expect_tx(&bt_full[stage], kTileBytes);
-        dst = bt_tiles + (size_t)stage * kTileBytes;
-        tma_load_2d(dst, tbt, &bt_full[stage], col0, 0);                     // b^T[0:128, col0 : col0+64]
-        tma_load_2d(dst + kPanelBytes, tbt, &bt_full[stage], col0 + 64, 0);  // b^T[0:128, col0+64 : col0+128]
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0 && ntiles > 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(kTile, kTile, 0, 0);
-      const uint32_t a_addr = smem_u32(a_tile);
-      mbar_wait(a_full, 0);
-      auto issue_s = [&](int t) {
-        const int stage = t % kBwdStages;
-        const uint32_t phase = (uint32_t)(t / kBwdStages) & 1u;
-        const int buf = t & 1;
-        const uint32_t bphase = (uint32_t)(t >> 1) & 1u;
-        mbar_wait(&s_empty[buf], bphase ^ 1u);
-        mbar_wait(&b_full[stage], phase);
-        tc_fence_after_sync();
-        issue_tile_mma(tmem_base + (uint32_t)buf * kTile, a_addr, smem_u32(b_tiles + (size_t)stage * kTileBytes),
-                       idesc, false);
-        umma_commit(&b_empty[stage]);
-        umma_commit(&s_full[buf]);
-      };
-      issue_s(0);
-      for (int t = 0; t < ntiles; ++t) {
-        if (t + 1 < ntiles) issue_s(t + 1);
-        const int stage = t % kBwdStages;
-        const uint32_t phase = (uint32_t)(t / kBwdStages) & 1u;
-        const int buf = t & 1;
-        const uint32_t bphase = (uint32_t)(t >> 1) & 1u;
-        mbar_wait(&p_full[buf], bphase);
-        mbar_wait(&bt_full[stage], phase);
-        tc_fence_after_sync();
-        issue_tile_mma(tmem_da, smem_u32(p_tiles + (size_t)buf * kTileBytes),
-                       smem_u32(bt_tiles + (size_t)stage * kTileBytes), idesc, t > 0);
-        umma_commit(&bt_empty[stage]);
-        umma_commit(&p_empty[buf]);
-      }
-      umma_commit(da_full);
-    }
-  } else {
-    const int q = warp & 3;
-    const int etid = q * 32 + lane;  // == accumulator row within the tile
-    const int64_t row = row0 + etid;
-    const float rinv = row < sd.Ma ? sd.rinv[row] : 0.f;
-    for (int t = 0; t < ntiles; ++t) {
-      const int buf = t & 1;
-      const uint32_t bphase = (uint32_t)(t >> 1) & 1u;
-      const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
-      float* cs = cinv_s + buf * kTile;
-      cs[etid] = (col0 + etid < sd.Nb) ? sd.cinv[col0 + etid] : 0.f;
-      named_bar_sync(1, kEpiThreads);
-      mbar_wait(&p_empty[buf], bphase ^ 1u);
-      mbar_wait(&s_full[buf], bphase);
-      tc_fence_after_sync();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * kTile;
-      uint8_t* p_tile = p_tiles + (size_t)buf * kTileBytes;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        uint32_t packed[16];
-#pragma unroll
-        for (int e = 0; e < 32; e += 2) {
-          const float2 cv = *reinterpret_cast<const float2*>(&cs[c * 32 + e]);
-          const float p0 = ex2_approx(__uint_as_float(r[e]) * kLog2e) * (rinv + cv.x);
-          const float p1 = ex2_approx(__uint_as_float(r[e + 1]) * kLog2e) * (rinv + cv.y);
-          __nv_bfloat162 h = __floats2bfloat162_rn(p0, p1);  // .x = p0 (low half) = lower column
-          packed[e >> 1] = *reinterpret_cast<uint32_t*>(&h);
-        }
-        // 32 columns = 64 B = four 16-byte chunks of panel (c >> 1), chunk index (c & 1) * 4 + i
-        uint8_t* panel = p_tile + (uint32_t)(c >> 1) * kPanelBytes;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const uint32_t off = sw128_offset((uint32_t)etid, (uint32_t)((c & 1) * 4 + i));
-          *reinterpret_cast<uint4*>(panel + off) =
-              make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
-        }
-      }
-      tc_fence_before_sync();
-      mbar_arrive(&s_empty[buf]);
-      fence_proxy_async_smem();
-      mbar_arrive(&p_full[buf]);
-    }
-    // ---- final: da accumulator -> global -----------------------------------------------------------------
-    if (ntiles > 0) {
-      mbar_wait(da_full, 0);
-      tc_fence_after_sync();
-    }
-    const float s = args.scale * (args.gscale ? args.gscale[0] : 1.0f);
-    const uint32_t taddr = tmem_da + ((uint32_t)(q * 32) << 16);
-    const int64_t prow = sd.diag_offset + row;
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-      uint32_t r[32];
-      if (ntiles > 0) {
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-      } else {
-#pragma unroll
-        for (int e = 0; e < 32; ++e) r[e] = 0u;
-      }
-      if (row < sd.Ma) {
-        if (args.direct) {
-          float* dst = sd.out + row * kDim + c * 32;
-          const __nv_bfloat16* bp = sd.b + prow * kDim + c * 32;
-#pragma unroll
-          for (int e = 0; e < 32; e += 4) {
-            const uint2 braw = *reinterpret_cast<const uint2*>(bp + e);
-            const __nv_bfloat162 b01 = *reinterpret_cast<const __nv_bfloat162*>(&braw.x);
-            const __nv_bfloat162 b23 = *reinterpret_cast<const __nv_bfloat162*>(&braw.y);
-            float4 o;
-            o.x = s * (__uint_as_float(r[e]) - 2.0f * __low2float(b01));
-            o.y = s * (__uint_as_float(r[e + 1]) - 2.0f * __high2float(b01));
-            o.z = s * (__uint_as_float(r[e + 2]) - 2.0f * __low2float(b23));
-            o.w = s * (__uint_as_float(r[e + 3]) - 2.0f * __high2float(b23));
-            *reinterpret_cast<float4*>(dst + e) = o;
-          }
-        } else {
-          float* dst = sd.out + ((int64_t)blockIdx.y * sd.Ma + row) * kDim + c * 32;
-#pragma unroll
-          for (int e = 0; e < 32; e += 4)
-            *reinterpret_cast<float4*>(dst + e) = make_float4(__uint_as_float(r[e]), __uint_as_float(r[e + 1]),
-                                                              __uint_as_float(r[e + 2]), __uint_as_float(r[e + 3]));
-        }
-      }
-    }
-  }
-  tc_fence_before_sync();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after_sync();
-    __syncwarp();
-    tmem_dealloc<512>(tmem_base);
-  }
-}
-
-// da[i, :] = s * (sum_k partial[k][i, :] - 2 b[pos(i), :])
-__global__ void grad_reduce_kernel(const float* __restrict__ partial, int nsplit, int64_t Ma, int64_t diag_offset,
-                                   const __nv_bfloat16* __restrict__ b, float scale, const float* __restrict__ gscale,
-                                   float* __restrict__ da) {
+// da[i, :] = s * (sum_k partial[k][i, :] - 2 b[pos(i), :]) for the column-split partials of the gradient kernel
+// (clip_tc2.cu); both sides of a step in one launch (blockIdx.y), partials added in split order.
+__global__ void grad_reduce_kernel(GradReduceSide s0, GradReduceSide s1, int nsplit, int64_t Ma, float scale,
+                                   const float* __restrict__ gscale) {
+  const GradReduceSide& sd = blockIdx.y == 0 ? s0 : s1;
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;  // float4 index
   if (i >= Ma * (kDim / 4)) return;
   const int64_t row = i / (kDim / 4);
   const int c4 = (int)(i % (kDim / 4)) * 4;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
   for (int k = 0; k < nsplit; ++k) {
-    const float4 v = *reinterpret_cast<const float4*>(partial + ((int64_t)k * Ma + row) * kDim + c4);
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(sd.partial + ((int64_t)k * Ma + row) * kDim + c4));
     acc.x += v.x;
     acc.y += v.y;
     acc.z += v.z;
     acc.w += v.w;
   }
-  const __nv_bfloat16* bp = b + (diag_offset + row) * kDim + c4;
+  const __nv_bfloat16* bp = static_cast<const __nv_bfloat16*>(sd.b) + (sd.diag_offset + row) * kDim + c4;
   const float s = scale * (gscale ? gscale[0] : 1.0f);
   float4 o;
   o.x = s * (acc.x - 2.0f * __bfloat162float(bp[0]));
   o.y = s * (acc.y - 2.0f * __bfloat162float(bp[1]));
   o.z = s * (acc.z - 2.0f * __bfloat162float(bp[2]));
   o.w = s * (acc.w - 2.0f * __bfloat162float(bp[3]));
-  *reinterpret_cast<float4*>(da + row * kDim + c4) = o;
-}
-
-size_t tc_grad_workspace(int64_t Ma, int64_t Nb) {
-  int ns, tps;
-  plan_split(Ma, Nb, 1, 8, &ns, &tps);
-  return ns > 1 ? 2 * align_up((size_t)ns * Ma * kDim * sizeof(float), 1024) + 2048 : 2048;
-}
-
-int tc_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, const float* gscale, void* ws,
-            size_t ws_bytes, cudaStream_t st) {
-  PCLIP_REQUIRE(D == kDim, PCLIP_ERR_UNSUPPORTED, "bf16 tensor-core path needs D == %d (got %d)", kDim, D);
-  for (int i = 0; i < n_sides; ++i) {
-    const pclip_clip_bwd_side_t& s = sides[i];
-    PCLIP_REQUIRE(s.a && s.b && s.bT && s.rinv && s.cinv && s.da && s.Ma > 0 && s.Nb > 0, PCLIP_ERR_INVALID,
-                  "grad: bad side %d (the bf16 path needs the transposed copy bT)", i);
-    PCLIP_REQUIRE(s.ldbT >= s.Nb && s.ldbT % 8 == 0, PCLIP_ERR_INVALID, "grad: ldbT must be >= Nb and a multiple of 8");
-    PCLIP_REQUIRE(s.diag_offset >= 0 && s.diag_offset + s.Ma <= s.Nb, PCLIP_ERR_INVALID,
-                  "grad: positives of side %d fall outside b", i);
-    PCLIP_REQUIRE(s.Ma == sides[0].Ma && s.Nb == sides[0].Nb, PCLIP_ERR_UNSUPPORTED,
-                  "grad: both sides must have the same shape");
-  }
-  const int64_t Ma = sides[0].Ma, Nb = sides[0].Nb;
-  int nsplit, tps;
-  plan_split(Ma, Nb, n_sides, 8, &nsplit, &tps);
-  Workspace w(ws, ws_bytes);
-  TcBwdArgs args;
-  CUtensorMap maps[6];
-  float* partial[2] = {nullptr, nullptr};
-  for (int i = 0; i < 2; ++i) {
-    const pclip_clip_bwd_side_t& s = sides[i < n_sides ? i : 0];
-    PCLIP_TRY(make_tmap_bf16_2d(&maps[3 * i], s.a, (uint64_t)s.Ma, kDim, kDim, kTile, 64));
-    PCLIP_TRY(make_tmap_bf16_2d(&maps[3 * i + 1], s.b, (uint64_t)s.Nb, kDim, kDim, kTile, 64));
-    PCLIP_TRY(make_tmap_bf16_2d(&maps[3 * i + 2], s.bT, kDim, (uint64_t)s.Nb, (uint64_t)s.ldbT, kTile, 64));
-    if (nsplit > 1 && i < n_sides) {
-      PCLIP_REQUIRE(ws, PCLIP_ERR_WORKSPACE, "grad: workspace required");
-      partial[i] = w.take<float>((size_t)nsplit * s.Ma * kDim);
-    }
-    args.s[i] = {s.Ma,   s.Nb,   s.diag_offset, s.rinv, s.cinv, static_cast<const __nv_bfloat16*>(s.b),
-                 nsplit > 1 ? partial[i] : s.da};
-  }
-  PCLIP_REQUIRE(nsplit == 1 || w.ok(), PCLIP_ERR_WORKSPACE, "grad: workspace too small");
-  args.tiles_per_split = tps;
-  args.direct = nsplit == 1;
-  args.scale = scale;
-  args.gscale = gscale;
-  PCLIP_CHECK_CUDA(
-      cudaFuncSetAttribute(tc_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmemBytes));
-  dim3 grid((unsigned)ceil_div(Ma, kTile), (unsigned)nsplit, (unsigned)n_sides);
-  tc_grad_kernel<<<grid, kThreads, kBwdSmemBytes, st>>>(maps[0], maps[1], maps[2], maps[3], maps[4], maps[5], args);
-  PCLIP_CHECK_LAUNCH();
-  if (nsplit > 1) {
-    for (int i = 0; i < n_sides; ++i) {
-      grad_reduce_kernel<<<(unsigned)ceil_div(Ma * (kDim / 4), 256), 256, 0, st>>>(
-          partial[i], nsplit, Ma, sides[i].diag_offset, static_cast<const __nv_bfloat16*>(sides[i].b), scale, gscale,
-          sides[i].da);
-      PCLIP_CHECK_LAUNCH();
-    }
-  }
-  return PCLIP_OK;
+  *reinterpret_cast<float4*>(sd.da + row * kDim + c4) = o;
 }
 
 }  // namespace pclip

@@ -1,7 +1,8 @@
-// Second-generation BF16 tensor-core kernels of the CLIP InfoNCE contractions (PCLIP_COMPUTE_BF16, D == 128).
+// BF16 tensor-core kernels of the CLIP InfoNCE contractions at configuration size (PCLIP_COMPUTE_BF16, D == 128): the
+// single-pass forward (tc2_sumexp_kernel) and the transposed-form gradient (tc3_grad_kernel).
 //   ref: modules/training_utils.py:85-89 (S = x @ y.T; exp; row / column sums; loss) and its autograd backward.
 //
-// Differences from clip_tc.cu (first generation, kept for A/B runs through PCLIP_CLIP_GEN=1):
+// Differences from the two-sided forward in clip_tc.cu (the path below 2048 columns):
 //   * 256-row CTAs: two 128-row UMMA tiles share every streamed column tile (half the L2 -> SMEM operand traffic).
 //   * the column tile is loaded ONCE: the second MMA of the gradient (P . Y) reads the same shared-memory tile as an
 //     MN-major B operand, so no transposed copy of the embeddings exists in HBM any more.
@@ -143,255 +144,8 @@ struct Tc2BwdArgs {
 };
 
 namespace c2 {
-constexpr int kBwdStages = 3;
-// A (2 tiles) | Y ring | P (2 tiles) | cinv staging [2][128] | barriers
-constexpr uint32_t kBwdSmem = kTileBytes * (kH + kBwdStages + kH) + 2 * kTile * 4 + 256 + 1024;
-static_assert(kBwdSmem <= 232448, "shared memory budget");
-constexpr int kBwdThreads = 64 + 32 * 16;
 constexpr int kPolyPerChunk = PCLIP_BWD_POLY;  // of every 32 exps, this many go to the FMA pipes (multiple of 2)
 }  // namespace c2
-
-__global__ void __launch_bounds__(c2::kBwdThreads, 1)
-tc2_grad_kernel(const __grid_constant__ CUtensorMap ta0, const __grid_constant__ CUtensorMap tb0,
-                const __grid_constant__ CUtensorMap ta1, const __grid_constant__ CUtensorMap tb1,
-                const Tc2BwdArgs args) {
-  using namespace c2;
-  const Tc2BwdSide& sd = args.s[blockIdx.z];
-  const CUtensorMap* ta = blockIdx.z == 0 ? &ta0 : &ta1;
-  const CUtensorMap* tb = blockIdx.z == 0 ? &tb0 : &tb1;
-  const int64_t row0 = (int64_t)blockIdx.x * kRows;
-  if (row0 >= sd.Ma) return;
-  const int nh = row0 + kTile < sd.Ma ? 2 : 1;
-  const int ntiles_all = (int)((sd.Nb + kTile - 1) / kTile);
-  const int tile_begin = blockIdx.y * args.tiles_per_split;
-  const int ntiles = max(min(tile_begin + args.tiles_per_split, ntiles_all) - tile_begin, 0);
-
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* a_tiles = smem;
-  uint8_t* y_tiles = a_tiles + kH * kTileBytes;
-  uint8_t* p_tiles = y_tiles + kBwdStages * kTileBytes;
-  // [2][128], indexed by tile parity.  Both row-tile groups write the SAME values for a tile; the MMA issue order
-  // keeps the groups within one tile of each other, so a slot is never rewritten while the other group reads it.
-  float* cinv_s = reinterpret_cast<float*>(p_tiles + kH * kTileBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(cinv_s + 2 * kTile);
-  uint64_t* a_full = bars;                    // 1
-  uint64_t* y_full = a_full + 1;              // kBwdStages
-  uint64_t* y_empty = y_full + kBwdStages;    // kBwdStages
-  uint64_t* s_full = y_empty + kBwdStages;    // [kH]
-  uint64_t* p_full = s_full + kH;             // [kH]
-  uint64_t* d_full = p_full + kH;             // 1
-  uint64_t* pv_done = d_full + 1;             // [kH]: the P . Y MMA of the previous tile has finished reading P_h
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + kH);
-
-  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
-  long long* tr = (args.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? args.trace : nullptr;
-  if (threadIdx.x == 0) {
-    mbar_init(a_full, 1);
-    for (int i = 0; i < kBwdStages; ++i) {
-      mbar_init(&y_full[i], 1);
-      mbar_init(&y_empty[i], 1);
-    }
-    for (int i = 0; i < kH; ++i) {
-      mbar_init(&s_full[i], 1);
-      mbar_init(&p_full[i], 256);
-      mbar_init(&pv_done[i], 1);
-    }
-    mbar_init(d_full, 1);
-    fence_mbar_init();
-  }
-  if (warp == 1) tmem_alloc<512>(tmem_slot);
-  tc_fence_before_sync();
-  __syncthreads();
-  tc_fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;   // columns [0,256): S of row tile 0 / 1; [256,512): dA of row tile 0 / 1
-
-  if (warp == 0) {
-    if (lane == 0) {
-      tma_prefetch_desc(ta);
-      tma_prefetch_desc(tb);
-      mbar_arrive_expect_tx(a_full, (uint32_t)nh * kTileBytes);
-      for (int h = 0; h < nh; ++h) {
-        tma_load_2d(a_tiles + h * kTileBytes, ta, a_full, 0, (int32_t)(row0 + h * kTile));
-        tma_load_2d(a_tiles + h * kTileBytes + kPanelBytes, ta, a_full, 64, (int32_t)(row0 + h * kTile));
-      }
-      for (int t = 0; t < ntiles; ++t) {
-        const int stage = t % kBwdStages;
-        const uint32_t phase = (uint32_t)(t / kBwdStages) & 1u;
-        mbar_wait(&y_empty[stage], phase ^ 1u);
-        mbar_arrive_expect_tx(&y_full[stage], kTileBytes);
-        const int32_t col0 = (tile_begin + t) * kTile;
-        uint8_t* dst = y_tiles + (size_t)stage * kTileBytes;
-        tma_load_2d(dst, tb, &y_full[stage], 0, col0);
-        tma_load_2d(dst + kPanelBytes, tb, &y_full[stage], 64, col0);
-      }
-    }
-  } else if (warp == 1) {
-    if (ntiles > 0) {   // the whole warp runs the issue loop; one elected lane issues each tcgen05 instruction
-      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, 0, 0);   // S = A . Y^T   (both K-major)
-      constexpr uint32_t idesc_g = make_idesc_bf16(kTile, kTile, 0, 1);   // dA += P . Y   (Y tile as MN-major B)
-      mbar_wait(a_full, 0);
-      auto issue_s = [&](int h, int t) {
-        const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kBwdStages) * kTileBytes);
-        const uint32_t a_addr = smem_u32(a_tiles + h * kTileBytes);
-        if (lane == 0) PCLIP_TRACE(0, 2 * t + h);
-        const uint64_t ad = kmajor_base(a_addr), yd = kmajor_base(y_addr);
-        if (elect_one()) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k)
-            umma_bf16_ss(tmem_base + (uint32_t)h * kTile, kmajor_step(ad, k), kmajor_step(yd, k), idesc_s, k > 0 ? 1u : 0u);
-          umma_commit(&s_full[h]);
-        }
-        __syncwarp();
-      };
-      mbar_wait(&y_full[0], 0);
-      tc_fence_after_sync();
-      for (int h = 0; h < nh; ++h) issue_s(h, 0);
-      for (int t = 0; t < ntiles; ++t) {
-        const uint32_t y_addr = smem_u32(y_tiles + (size_t)(t % kBwdStages) * kTileBytes);
-        for (int h = 0; h < nh; ++h) {
-          mbar_wait(&p_full[h], (uint32_t)t & 1u);        // P_h(t) written => S_h(t) fully consumed
-          tc_fence_after_sync();
-          // the next score tile of this half goes FIRST: its epilogue is the critical path (epilogue -> P.Y -> S ->
-          // epilogue was one serial chain per half, r01c profile); P_h stays protected by pv_done[h]
-          if (t + 1 < ntiles) {
-            if (h == 0) {
-              const int st = (t + 1) % kBwdStages;
-              mbar_wait(&y_full[st], (uint32_t)((t + 1) / kBwdStages) & 1u);
-              tc_fence_after_sync();
-            }
-            issue_s(h, t + 1);
-          }
-          const uint32_t p_addr = smem_u32(p_tiles + h * kTileBytes);
-          if (lane == 0) PCLIP_TRACE(1, 2 * t + h);
-          const uint64_t pd = kmajor_base(p_addr), yd = mnmajor_base(y_addr);
-          if (elect_one()) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k)
-              umma_bf16_ss(tmem_base + (uint32_t)(kH + h) * kTile, kmajor_step(pd, k), mnmajor_step(yd, k), idesc_g,
-                           (t > 0 || k > 0) ? 1u : 0u);
-            umma_commit(&pv_done[h]);
-            if (h == nh - 1) umma_commit(&y_empty[t % kBwdStages]);
-            if (h == nh - 1 && t == ntiles - 1) umma_commit(d_full);
-          }
-          __syncwarp();
-        }
-      }
-    }
-  } else {
-    // 16 epilogue warps: row half h x lane quadrant q x column half ch (4 warps per SM sub-partition)
-    const int h = (warp - 2) >> 3, ch = ((warp - 2) >> 2) & 1, q = warp & 3;
-    const int i = q * 32 + lane;                       // row inside the tile
-    const int64_t row = row0 + h * kTile + i;
-    const bool live = h < nh;
-    if (live) {
-      const float rinv = row < sd.Ma ? sd.rinv[row] : 0.f;
-      const uint64_t rinv2 = pack2(rinv, rinv);
-      const uint32_t p_addr = smem_u32(p_tiles + h * kTileBytes) + (uint32_t)ch * kPanelBytes;   // my 64-column panel
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)h * kTile + (uint32_t)ch * 64u;
-      for (int t = 0; t < ntiles; ++t) {
-        const int64_t col0 = (int64_t)(tile_begin + t) * kTile;
-        float* cs = cinv_s + (t & 1) * kTile;
-        if (ch == 0) cs[i] = (col0 + i < sd.Nb) ? sd.cinv[col0 + i] : 0.f;   // 0 also masks the zero-filled columns beyond Nb
-        const bool tracer = (threadIdx.x & 255) == 64;   // first thread of each half's first warp
-        if (tracer) PCLIP_TRACE(2, 2 * t + h);
-        named_bar_sync(1 + h, 256);
-        mbar_wait(&s_full[h], (uint32_t)t & 1u);
-        tc_fence_after_sync();
-        if (tracer) PCLIP_TRACE(3, 2 * t + h);
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(taddr + c * 32, v);
-          const uint32_t cs_addr = smem_u32(cs + ch * 64 + c * 32);   // explicit shared-space loads (see tc3_grad_kernel)
-          uint64_t cs2[16];
-#pragma unroll
-          for (int e = 0; e < 32; e += 4)
-            asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(cs2[e >> 1]), "=l"(cs2[(e >> 1) + 1]) : "r"(cs_addr + 4u * e) : "memory");
-          tmem_ld_wait();
-          uint32_t packed[16];
-#pragma unroll
-          for (int e = 0; e < 32; e += 2) {
-            float e0, e1;
-            if (e < kPolyPerChunk) {
-              exp_poly2<3>(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), e0, e1);
-            } else {
-              float y0, y1;
-              unpack2(mul2(pack2(__uint_as_float(v[e]), __uint_as_float(v[e + 1])), pack2(kLog2e, kLog2e)), y0, y1);
-              e0 = ex2_approx(y0);
-              e1 = ex2_approx(y1);
-            }
-            const uint64_t w = add2(rinv2, cs2[e >> 1]);
-            float p0, p1;
-            unpack2(mul2(pack2(e0, e1), w), p0, p1);
-            packed[e >> 1] = bf16x2_bits(p0, p1);
-          }
-          if (c == 0 && tracer) PCLIP_TRACE(4, 2 * t + h);
-          if (c == 0 && t > 0) mbar_wait(&pv_done[h], (uint32_t)(t - 1) & 1u);   // P_h(t-1) has been consumed
-          if (c == 0 && tracer) PCLIP_TRACE(5, 2 * t + h);
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            st_shared_v4(p_addr + sw128_offset((uint32_t)i, (uint32_t)(c * 4 + g)), packed[4 * g], packed[4 * g + 1],
-                         packed[4 * g + 2], packed[4 * g + 3]);
-        }
-        tc_fence_before_sync();
-        fence_proxy_async_smem();
-        mbar_arrive(&p_full[h]);
-        if (tracer) PCLIP_TRACE(6, 2 * t + h);
-      }
-      if (ntiles > 0) {
-        mbar_wait(d_full, 0);
-        tc_fence_after_sync();
-      }
-      // ---- final: dA accumulator -> global (every lane loads: tcgen05.ld is warp-collective) ----
-      const float s = args.scale * (args.gscale ? args.gscale[0] : 1.0f);
-      const uint32_t daddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(kH + h) * kTile + (uint32_t)ch * 64u;
-      const int64_t prow = sd.diag_offset + row;
-#pragma unroll 1
-      for (int c = 0; c < 2; ++c) {
-        uint32_t r[32];
-        if (ntiles > 0) {
-          tmem_ld_32x32b_x32(daddr + c * 32, r);
-          tmem_ld_wait();
-        } else {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) r[e] = 0u;
-        }
-        if (row < sd.Ma) {
-          if (args.direct) {
-            float* dst = sd.out + row * kDim + ch * 64 + c * 32;
-            const __nv_bfloat16* bp = sd.b + prow * kDim + ch * 64 + c * 32;
-#pragma unroll
-            for (int e = 0; e < 32; e += 4) {
-              const uint2 braw = *reinterpret_cast<const uint2*>(bp + e);
-              const __nv_bfloat162 b01 = *reinterpret_cast<const __nv_bfloat162*>(&braw.x);
-              const __nv_bfloat162 b23 = *reinterpret_cast<const __nv_bfloat162*>(&braw.y);
-              float4 o;
-              o.x = s * (__uint_as_float(r[e]) - 2.0f * __low2float(b01));
-              o.y = s * (__uint_as_float(r[e + 1]) - 2.0f * __high2float(b01));
-              o.z = s * (__uint_as_float(r[e + 2]) - 2.0f * __low2float(b23));
-              o.w = s * (__uint_as_float(r[e + 3]) - 2.0f * __high2float(b23));
-              *reinterpret_cast<float4*>(dst + e) = o;
-            }
-          } else {
-            float* dst = sd.out + ((int64_t)blockIdx.y * sd.Ma + row) * kDim + ch * 64 + c * 32;
-#pragma unroll
-            for (int e = 0; e < 32; e += 4)
-              *reinterpret_cast<float4*>(dst + e) = make_float4(__uint_as_float(r[e]), __uint_as_float(r[e + 1]),
-                                                                __uint_as_float(r[e + 2]), __uint_as_float(r[e + 3]));
-          }
-        }
-      }
-    }
-  }
-  tc_fence_before_sync();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after_sync();
-    __syncwarp();
-    tmem_dealloc<512>(tmem_base);
-  }
-}
 
 // =================================================================================================================
 // gradient, transposed formulation (third generation): both contractions are issued with N = 256.
@@ -943,9 +697,8 @@ tc2_sumexp_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant_
 // =================================================================================================================
 // host side
 // =================================================================================================================
-__global__ void grad_reduce_kernel(const float* __restrict__ partial, int nsplit, int64_t Ma, int64_t diag_offset,
-                                   const __nv_bfloat16* __restrict__ b, float scale, const float* __restrict__ gscale,
-                                   float* __restrict__ da);
+__global__ void grad_reduce_kernel(GradReduceSide s0, GradReduceSide s1, int nsplit, int64_t Ma, float scale,
+                                   const float* __restrict__ gscale);
 __global__ void sum_partials_kernel(const float* __restrict__ partial, int nsplit, int64_t M, float* __restrict__ out);
 
 // colsum[j] = sum_r colpart[r][j] + exp(diag[j - off]) for the columns that are some local row's positive
@@ -954,7 +707,15 @@ __global__ void col_reduce_kernel(const float* __restrict__ colpart, int nrb, in
   const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (j >= Nb) return;
   float s = 0.f;
-  for (int r = 0; r < nrb; ++r) s += colpart[(int64_t)r * Nb + j];
+  int r = 0;
+  for (; r + 8 <= nrb; r += 8) {           // eight loads in flight, added in row-block order
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = __ldcs(colpart + (int64_t)(r + u) * Nb + j);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) s += v[u];
+  }
+  for (; r < nrb; ++r) s += colpart[(int64_t)r * Nb + j];
   if (j >= off && j < off + Ma) s += expf(diag[j - off]);
   colsum[j] = s;
 }
@@ -1039,18 +800,8 @@ int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale
     PCLIP_CHECK_CUDA(cudaMemsetAsync(args.trace, 0, 8 * kTraceItems * sizeof(long long), st));
   }
   dim3 grid((unsigned)ceil_div(Ma, kRows), (unsigned)nsplit, (unsigned)n_sides);
-  // PCLIP_GRAD_FORM=rows selects the row-major formulation (N = 128 MMAs, kept for A/B runs); default: transposed
-  static const bool transposed = [] {
-    const char* e = getenv("PCLIP_GRAD_FORM");
-    return !(e && e[0] == 'r');
-  }();
-  if (transposed) {
-    PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc3_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c3::kSmem3));
-    tc3_grad_kernel<<<grid, c3::kThreads3, c3::kSmem3, st>>>(maps[0], maps[1], maps[2], maps[3], args);
-  } else {
-    PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc2_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmem));
-    tc2_grad_kernel<<<grid, kBwdThreads, kBwdSmem, st>>>(maps[0], maps[1], maps[2], maps[3], args);
-  }
+  PCLIP_CHECK_CUDA(cudaFuncSetAttribute(tc3_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c3::kSmem3));
+  tc3_grad_kernel<<<grid, c3::kThreads3, c3::kSmem3, st>>>(maps[0], maps[1], maps[2], maps[3], args);
   PCLIP_CHECK_LAUNCH();
   if (args.trace) {   // debug only: synchronises
     static long long h[8 * kTraceItems];
@@ -1069,12 +820,14 @@ int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale
     }
   }
   if (nsplit > 1) {
-    for (int i = 0; i < n_sides; ++i) {
-      grad_reduce_kernel<<<(unsigned)ceil_div(Ma * (kDim / 4), 256), 256, 0, st>>>(
-          partial[i], nsplit, Ma, sides[i].diag_offset, static_cast<const __nv_bfloat16*>(sides[i].b), scale, gscale,
-          sides[i].da);
-      PCLIP_CHECK_LAUNCH();
+    GradReduceSide r[2];
+    for (int i = 0; i < 2; ++i) {
+      const pclip_clip_bwd_side_t& sd = sides[i < n_sides ? i : 0];
+      r[i] = {partial[i < n_sides ? i : 0], sd.b, sd.da, sd.diag_offset};
     }
+    grad_reduce_kernel<<<dim3((unsigned)ceil_div(Ma * (kDim / 4), 256), (unsigned)n_sides), 256, 0, st>>>(
+        r[0], r[1], nsplit, Ma, scale, gscale);
+    PCLIP_CHECK_LAUNCH();
   }
   return PCLIP_OK;
 }

@@ -88,19 +88,21 @@ int simt_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scal
 size_t tc_rowsumexp_workspace(int64_t Ma, int64_t Nb);
 int tc_rowsumexp(const pclip_clip_fwd_side_t* sides, int n_sides, int D, void* ws, size_t ws_bytes,
                  cudaStream_t st);
-size_t tc_grad_workspace(int64_t Ma, int64_t Nb);
-int tc_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, const float* gscale, void* ws,
-            size_t ws_bytes, cudaStream_t st);
+// one side of the reduction of the gradient kernel's column-split partials (clip_tc.cu: grad_reduce_kernel)
+struct GradReduceSide {
+  const float* partial;       // [nsplit][Ma][128]
+  const void* b;              // packed bf16 [Nb, 128] (the -2 b_pos term)
+  float* da;                  // [Ma, 128]
+  int64_t diag_offset;
+};
 
-// second-generation BF16 kernels (clip_tc2.cu)
+// single-pass forward and gradient kernels (clip_tc2.cu)
 size_t tc2_grad_workspace(int64_t Ma, int64_t Nb);
 int tc2_grad(const pclip_clip_bwd_side_t* sides, int n_sides, int D, float scale, const float* gscale, void* ws,
              size_t ws_bytes, cudaStream_t st);
 size_t tc2_sumexp_workspace(int64_t Ma, int64_t Nb);
 int tc2_sumexp(const void* a, const void* b, int64_t Ma, int64_t Nb, int64_t diag_offset, int D, float* rowsum,
                float* colsum, float* diag, void* ws, size_t ws_bytes, cudaStream_t st);
-// 1 = first-generation CLIP kernels (PCLIP_CLIP_GEN=1), else second generation
-int clip_generation();
 // BF16 tcgen05 candidate selection + fp32 re-scoring (topk_tc.cu)
 size_t tc_topk_workspace(int64_t Q, int64_t N, int k);
 int tc_topk(const float* q, const float* bank, int64_t Q, int64_t N, int D, int k, int64_t index_base, int64_t* idx,

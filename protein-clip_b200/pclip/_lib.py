@@ -50,6 +50,7 @@ SIGNATURES = {
     "pclip_normalize_scale_fwd": (C.c_int, [_P, _I64, _I32, _P, _F, _P, _P, _P]),
     "pclip_rowsum_workspace_bytes": (_SZ, [_I64]),
     "pclip_normalize_scale_bwd": (C.c_int, [_P, _P, _P, _I64, _I32, _P, _P, _P, _P, _SZ, _P]),
+    "pclip_pack_pair": (C.c_int, [C.POINTER(Chunk), _I32, C.POINTER(Chunk), _I32, _I32, _I64, _I32, _I32, _P, _P, _P]),
     "pclip_pack": (C.c_int, [C.POINTER(Chunk), _I32, _I32, _I64, _I32, _I32, _P, _P, _I64, _P]),
     "pclip_transpose_bf16": (C.c_int, [_P, _I64, _I32, _P, _I64, _P]),
     "pclip_clip_rowsumexp_workspace_bytes": (_SZ, [_I64, _I64, _I32, _I32]),
@@ -57,7 +58,8 @@ SIGNATURES = {
     "pclip_clip_sumexp_workspace_bytes": (_SZ, [_I64, _I64, _I32, _I32]),
     "pclip_clip_sumexp": (C.c_int, [_P, _P, _I64, _I64, _I64, _I32, _I32, _P, _P, _P, _P, _SZ, _P]),
     "pclip_clip_finalize": (C.c_int, [_P, _P, _P, _I64, _F, _P, _P, _P, _P, _P, _P]),
-    "pclip_clip_finalize_sharded": (C.c_int, [_P, _I32, _I64, _I64, _F, _P, _P, _P, _P, _P, _P, _P]),
+    "pclip_clip_finalize_sharded_workspace_bytes": (_SZ, [_I64]),
+    "pclip_clip_finalize_sharded": (C.c_int, [_P, _I32, _I64, _I64, _F, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "pclip_clip_grad_workspace_bytes": (_SZ, [_I64, _I64, _I32, _I32]),
     "pclip_clip_grad": (C.c_int, [C.POINTER(BwdSide), _I32, _I32, _I32, _F, _P, _P, _SZ, _P]),
     "pclip_clip_workspace_bytes": (_SZ, [_I64, _I32, _I32]),

@@ -271,13 +271,11 @@ class ClipPlan:
         self.xf = self.xl if self.local_is_full else torch.empty(Nb, D, dtype=self.cdt, device=dev)
         self.yf = self.yl if self.local_is_full else torch.empty(Nb, D, dtype=self.cdt, device=dev)
         # second-generation bf16 kernels: single-pass forward (row AND column sums from one sweep over S) and a
-        # gradient kernel that needs no transposed operand copies; PCLIP_CLIP_GEN=1 selects the first generation
+        # gradient kernel that needs no transposed operand copies
         # (below SINGLE_PASS_MIN_COLS columns the two-sided forward is used: its column sums are fp32-exact, whereas the
         # single pass sums bf16-rounded exps -- errors that average out over thousands of rows but not over 16)
-        self.single_pass = tc and os.environ.get("PCLIP_CLIP_GEN", "2") != "1" and Nb >= SINGLE_PASS_MIN_COLS
-        need_T = tc and os.environ.get("PCLIP_CLIP_GEN", "2") == "1"
-        self.xfT = torch.zeros(D, self.ldT, dtype=self.cdt, device=dev) if need_T else None
-        self.yfT = torch.zeros(D, self.ldT, dtype=self.cdt, device=dev) if need_T else None
+        self.single_pass = tc and Nb >= SINGLE_PASS_MIN_COLS
+        self.xfT = self.yfT = None      # no kernel reads transposed operand copies any more (fields kept in the ABI)
         self.rowsum, self.colsum = torch.empty(Ma, **f32), torch.empty(Ma, **f32)
         # single-pass: column sums of ALL Nb columns over this plan's rows (partial under row sharding)
         self.colsum_f = self.colsum if self.local_is_full else torch.empty(Nb, **f32)
@@ -287,18 +285,26 @@ class ClipPlan:
         # 1/R and 1/C of ALL rows (the gradient kernel needs the other side's normalisers for every column)
         self.rinv_f = self.rinv if self.local_is_full else torch.empty(Nb, **f32)
         self.cinv_f = self.cinv if self.local_is_full else torch.empty(Nb, **f32)
-        if self.single_pass and not self.local_is_full:
-            # Row shard: what this rank owes the others after the forward sweep is ONE contiguous record
-            # [C partial (Nb) | R (Ma) | S_ii (Ma)] (pclip/sharded.py gathers it in one collective); the forward kernel
-            # writes straight into it, and 1/R, 1/C of the local rows are views of the full-length results.
+        if self.single_pass:
+            # What the forward sweep produces is ONE contiguous record [C partial (Nb) | R (Ma) | S_ii (Ma)]: a row shard
+            # owes it to the other ranks (pclip/sharded.py gathers it in one collective), and pclip_clip_finalize_sharded
+            # turns P such records (P = 1 on one GPU: the same kernel, the same summation order, the same loss bits)
+            # into the loss and 1/R, 1/C of ALL rows; the local 1/R, 1/C are views of the full-length results.
             self.stats_l = torch.zeros(Nb + 2 * Ma, **f32)
             self.colsum_f = self.stats_l[:Nb]
             self.rowsum = self.stats_l[Nb:Nb + Ma]
             self.diag = self.stats_l[Nb + Ma:]
-            self.diag_full = torch.empty(Nb, **f32)
             self.row_lse_f, self.col_lse_f = torch.empty(Nb, **f32), torch.empty(Nb, **f32)
+            self.rinv_f, self.cinv_f = torch.empty(Nb, **f32), torch.empty(Nb, **f32)
             self.rinv = self.rinv_f[diag_offset:diag_offset + Ma]
             self.cinv = self.cinv_f[diag_offset:diag_offset + Ma]
+            self.row_lse = self.row_lse_f[diag_offset:diag_offset + Ma]
+            self.col_lse = self.col_lse_f[diag_offset:diag_offset + Ma]
+            if self.local_is_full:
+                self.colsum = self.colsum_f
+            with torch.cuda.device(dev):
+                self.fin_bytes = int(L.lib().pclip_clip_finalize_sharded_workspace_bytes(Nb))
+            self._fin_owner, self.fin_ws = L.workspace(self.fin_bytes, dev)
         self.loss = torch.zeros(1, **f32)
         self.dx, self.dy = torch.empty(Ma, D, **f32), torch.empty(Ma, D, **f32)
         lib = L.lib()
@@ -325,6 +331,11 @@ class ClipPlan:
         lib = L.lib()
         xs, ys = _limit_chunks(_as_rows(xs)), _limit_chunks(_as_rows(ys))
         full = self.local_is_full
+        if self.xfT is None and xs[0].dtype == ys[0].dtype:      # both modalities, one launch
+            L.check(lib.pclip_pack_pair(L.chunks_of(xs), len(xs), L.chunks_of(ys), len(ys), L.dtype_code(xs[0].dtype),
+                                        self.Ma, self.D, L.dtype_code(self.cdt), L.ptr(self.xl), L.ptr(self.yl),
+                                        self._st()))
+            return
         for src, out, outT in ((xs, self.xl, self.xfT if full else None), (ys, self.yl, self.yfT if full else None)):
             L.check(lib.pclip_pack(L.chunks_of(src), len(src), L.dtype_code(src[0].dtype), self.Ma, self.D,
                                    L.dtype_code(self.cdt), L.ptr(out), L.ptr(outT), self.ldT, self._st()))
@@ -360,6 +371,8 @@ class ClipPlan:
     @_on_device
     def finalize(self, B_total: int):
         """loss[0] = 1/(2B) sum_i (log R_i + log C_i - 2 S_ii) over the local rows; 1/R, 1/C for the backward."""
+        if self.single_pass and self.local_is_full:
+            return self.finalize_full(self.stats_l.view(1, -1), B_total)
         L.check(L.lib().pclip_clip_finalize(L.ptr(self.rowsum), L.ptr(self.colsum), L.ptr(self.diag), self.Ma,
                                             0.5 / B_total, L.ptr(self.row_lse), L.ptr(self.col_lse), L.ptr(self.rinv),
                                             L.ptr(self.cinv), L.ptr(self.loss), self._st()))
@@ -371,8 +384,8 @@ class ClipPlan:
         global on every rank and 1/R, 1/C of every row are local, so no further exchange is needed."""
         L.check(L.lib().pclip_clip_finalize_sharded(L.ptr(stats_all), stats_all.shape[0], self.Nb, self.Ma,
                                                     0.5 / B_total, L.ptr(self.row_lse_f), L.ptr(self.col_lse_f),
-                                                    L.ptr(self.rinv_f), L.ptr(self.cinv_f), L.ptr(self.diag_full),
-                                                    L.ptr(self.loss), self._st()))
+                                                    L.ptr(self.rinv_f), L.ptr(self.cinv_f), L.ptr(self.loss),
+                                                    self.fin_ws, self.fin_bytes, self._st()))
 
     @_on_device
     def grad(self, B_total: int, gscale: torch.Tensor | None = None):

@@ -7,6 +7,9 @@ from torch.profiler import profile, ProfilerActivity
 import bench
 d = bench.Dist(int(os.environ.get("WORLD_SIZE", "1")))
 w = bench.ClipLarge(d)
+w.record = False
+if os.environ.get("TIMELINE_GRAPH", "1") == "1":
+    print("graph:", w.enable_graph(), flush=True) if d.rank == 0 else w.enable_graph()
 for _ in range(5):
     w.step()
 torch.cuda.synchronize(); d.barrier()
