@@ -221,8 +221,8 @@ class ClipLarge:
             self._run(self.x, self.y)
 
     def enable_graph(self):
-        """N > 1: replay the whole sharded step (pack, 2 NCCL collectives, sweep, finalize, gradient) as ONE CUDA graph
-        launch: at 8 GPUs the ~25 host-side launches of a 0.8 ms step otherwise leave the GPU idle between kernels."""
+        """N > 1: replay the whole sharded step (pack, 2 NCCL collectives, peer copies, sweep, finalize, gradient) as ONE
+        CUDA graph launch: at 8 GPUs the host-side launches of a 0.7 ms step otherwise leave the GPU idle between kernels."""
         if self.job is None or os.environ.get("PCLIP_BENCH_GRAPH", "1") == "0":
             return False
         try:
@@ -263,13 +263,15 @@ class ClipLarge:
         main.wait_event(self.copied[b])
         self._ready[b] = False
         self._issue_copy(1 - b)       # the other buffer's last reader finished before the previous step's loss read
-        # (eager launches here: a graph replay would need the staged input copied into the captured tensors first, and
-        #  at 8 GPUs that hand-over costs more than the launches it saves: 1.09 vs 1.03 ms per step)
-        self.record, rec = True, self.record
-        self.record = False
-        g, self.graph = self.graph, None
-        loss, _, _ = self._run(self.sx2[b], self.sy2[b])
-        self.graph, self.record = g, rec
+        if self.graph is not None:    # N > 1: one captured graph per staging buffer (the graph reads the buffer in place)
+            if getattr(self, "graph_e2e", None) is None:
+                self.graph_e2e = [self.job.capture_graph([self.sx2[i]], [self.sy2[i]]) for i in (0, 1)]
+            self.graph_e2e[b][0].replay()
+            loss = self.graph_e2e[b][1][0]
+        else:
+            rec, self.record = self.record, False
+            loss, _, _ = self._run(self.sx2[b], self.sy2[b])
+            self.record = rec
         self.host_loss.copy_(loss, non_blocking=True)
         main.synchronize()            # the caller reads the loss (ref: loss.item(), :72)
         self._cur = 1 - b
@@ -890,9 +892,11 @@ def main():
         "e2e": {"value": round(e2e, 1), "unit": w.unit, "h2d_bytes_per_step": w.h2d * dist.world,
                 "d2h_bytes_per_step": w.d2h * dist.world, "ms_per_step": round(ms_e2e / args.steps, 4),
                 "pipeline": "H2D of step i+1 on a copy stream under step i (2 staging buffers); K copies inside the K "
-                            "timed steps" if hasattr(w, "e2e_begin") else "serial"},
+                            "timed steps" + ("; one captured graph per staging buffer" if graphed else "")
+                            if hasattr(w, "e2e_begin") else "serial"},
         "gpu_launches": launches, "check": check,
-        "launch_mode": ("one CUDA graph replay per step (capture of pack + 2 NCCL collectives + sweep + finalize + gradient); "
+        "launch_mode": ("one CUDA graph replay per step (capture of pack, Y all-gather, X peer copies on a side stream, "
+                        "forward sweep, record all-gather, finalize, gradient); "
                         f"eager launches: {ms_eager / args.steps:.4f} ms/step" if graphed else
                         "eager" + (f" (graph capture failed: {w.graph_error})" if w.graph_error else "")),
         "step_tflops_algorithmic": round(6.0 * w.B * w.B * w.D / (ms / args.steps * 1e-3) / 1e12, 1),

@@ -157,9 +157,10 @@ class ShardedClip:
     # idle between them.  All buffers of a step are owned by the plan, so the whole step -- pack, both collectives,
     # forward sweep, finalize, gradient -- is captured once and replayed with one launch.
     # -----------------------------------------------------------------------------------------------------
-    def capture(self, xs, ys, gscale=None):
-        """Capture step(xs, ys) into a CUDA graph.  xs / ys (and gscale) must be the tensors every later replay reads
-        (fill them in place before replay()).  Returns self."""
+    def capture_graph(self, xs, ys, gscale=None):
+        """Capture step(xs, ys) into a CUDA graph and return (graph, outputs).  Several graphs over different input
+        tensors (e.g. the two staging buffers of a prefetching loader) may be captured; they share the plan's buffers,
+        so their replays must be stream-ordered."""
         dev = self.s.dev
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -168,9 +169,15 @@ class ShardedClip:
                 self.step(xs, ys, gscale)
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
-        self._graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self._graph):
-            self._out = self.step(xs, ys, gscale)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = self.step(xs, ys, gscale)
+        return graph, out
+
+    def capture(self, xs, ys, gscale=None):
+        """Capture step(xs, ys) into a CUDA graph.  xs / ys (and gscale) must be the tensors every later replay reads
+        (fill them in place before replay()).  Returns self."""
+        self._graph, self._out = self.capture_graph(xs, ys, gscale)
         return self
 
     def replay(self):
