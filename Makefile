@@ -17,7 +17,16 @@ build/%.o: $(CSRC)/%.cu $(wildcard $(CSRC)/*.cuh) include/pclip.h
 $(LIB): $(OBJS)
 	$(NVCC) $(ARCH) -shared -cudart static -o $@ $(OBJS)
 
+# Race / barrier / memory checks of the smoke step (needs a GPU): every kernel family once, small shapes.
+# (compute-sanitizer is closed on the build pool's GPU boxes -- the target is for a maintainer's own machine.)
+SANITIZER ?= /usr/local/cuda/bin/compute-sanitizer
+sanitize: $(LIB)
+	@for t in memcheck racecheck synccheck; do \
+	  echo "== compute-sanitizer --tool $$t"; \
+	  $(SANITIZER) --tool $$t --error-exitcode 1 python -c "import __graft_entry__ as g; g.smoke()" || exit 1; \
+	done
+
 clean:
 	rm -rf build $(LIB)
 
-.PHONY: all clean
+.PHONY: all clean sanitize
