@@ -272,6 +272,18 @@ int pclip_rowwise_infonce(const float* logits, int64_t B, int64_t Bc, int64_t di
                           void* workspace /* pclip_rowsum_workspace_bytes(B) */, size_t workspace_bytes,
                           pclip_stream_t stream);
 
+/* pclip_rowwise_infonce for callers that cannot allocate or own a workspace (CUDA graph capture, serving loops):
+ * same arguments, arithmetic, summation order and results, but the scratch of the ordered loss sum lives in a
+ * file-scope static __device__ array of the library (16.6 KB, held by every GPU that loads the library until exit).
+ * No counterpart in the reference.
+ * Limit: B <= pclip_rowwise_infonce_noalloc_max_rows() = 32768, larger B returns PCLIP_ERR_UNSUPPORTED.  Calls no
+ * cudaMalloc / cudaFree.  All calls on one device share the array: calls that overlap on the GPU (different streams,
+ * no ordering between them) race; order them or use pclip_rowwise_infonce with one workspace per stream. */
+int64_t pclip_rowwise_infonce_noalloc_max_rows(void);
+int pclip_rowwise_infonce_noalloc(const float* logits, int64_t B, int64_t Bc, int64_t diag_offset, float scale,
+                                  float* loss /* [1], accumulated */, float* dlogits /* [B,Bc] or NULL */,
+                                  pclip_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -3,6 +3,8 @@
 #include <cuda_bf16.h>
 #include <float.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace pclip {
@@ -421,6 +423,34 @@ __global__ void rowwise_infonce_kernel(const float* __restrict__ logits, int64_t
   ordered_grid_sum(v, scratch, scale, loss);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Scratch of pclip_rowwise_infonce_noalloc: the per-block partials + ticket of the ordered grid sum for up to
+// kNoAllocMaxRows rows, resident in every GPU that loads the library (16 KB + 256 B).  In HOST code `g_noalloc_scratch`
+// is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once per device.
+// ---------------------------------------------------------------------------------------------
+constexpr int64_t kNoAllocMaxRows = 32768;
+constexpr int kNoAllocFloats = (int)(kNoAllocMaxRows / 8) + 64;      // one partial per block of 8 rows + the ticket
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
+
+constexpr int kNoAllocMaxDevices = 64;
+static float* g_noalloc_ptr[kNoAllocMaxDevices];                    // device address of the array, per device ordinal
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch(float** out) {
+  int dev = -1;
+  PCLIP_CHECK_CUDA(cudaGetDevice(&dev));
+  PCLIP_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, PCLIP_ERR_UNSUPPORTED, "noalloc: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    PCLIP_CHECK_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));   // of the CURRENT device's copy of the array
+    PCLIP_REQUIRE(p != nullptr, PCLIP_ERR_CUDA, "noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return PCLIP_OK;
+}
+
 }  // namespace pclip
 
 using namespace pclip;
@@ -552,6 +582,29 @@ int pclip_rowwise_infonce(const float* logits, int64_t B, int64_t Bc, int64_t di
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* scratch = nullptr;
   PCLIP_TRY(zero_ticket(workspace, workspace_bytes, B, st, &scratch));
+  const int threads = 256;
+  rowwise_infonce_kernel<<<(unsigned)ceil_div(B * 32, threads), threads, 0, st>>>(logits, B, Bc, diag_offset, scale, loss,
+                                                                                dlogits, scratch);
+  PCLIP_CHECK_LAUNCH();
+  return PCLIP_OK;
+}
+
+int64_t pclip_rowwise_infonce_noalloc_max_rows(void) { return kNoAllocMaxRows; }
+
+int pclip_rowwise_infonce_noalloc(const float* logits, int64_t B, int64_t Bc, int64_t diag_offset, float scale, float* loss,
+                                  float* dlogits, pclip_stream_t stream) {
+  PCLIP_TRY(require_device());
+  PCLIP_REQUIRE(logits && loss && B > 0 && Bc > 0 && diag_offset >= 0 && diag_offset + B <= Bc, PCLIP_ERR_INVALID,
+                "rowwise_infonce_noalloc: bad argument");
+  PCLIP_REQUIRE(B <= kNoAllocMaxRows, PCLIP_ERR_UNSUPPORTED,
+                "rowwise_infonce_noalloc: B = %lld exceeds the static scratch (at most %lld rows); use "
+                "pclip_rowwise_infonce with a caller-owned workspace", (long long)B, (long long)kNoAllocMaxRows);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* scratch = nullptr;
+  PCLIP_TRY(noalloc_scratch(&scratch));
+  // the array keeps the previous call's contents: the partials are overwritten before they are read, the ticket
+  // must start at zero
+  PCLIP_CHECK_CUDA(cudaMemsetAsync(scratch + ceil_div(B, 8), 0, sizeof(unsigned), st));
   const int threads = 256;
   rowwise_infonce_kernel<<<(unsigned)ceil_div(B * 32, threads), threads, 0, st>>>(logits, B, Bc, diag_offset, scale, loss,
                                                                                 dlogits, scratch);

@@ -83,6 +83,8 @@ SIGNATURES = {
     "pclip_filip_fwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _I32, _P, _P, _P, _P, _P, _SZ, _P]),
     "pclip_filip_bwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P,
                                   _P, _P, _SZ, _P]),
+    "pclip_rowwise_infonce_noalloc_max_rows": (_I64, []),
+    "pclip_rowwise_infonce_noalloc": (C.c_int, [_P, _I64, _I64, _I64, _F, _P, _P, _P]),
     "pclip_rowwise_infonce": (C.c_int, [_P, _I64, _I64, _I64, _F, _P, _P, _P, _SZ, _P]),
 }
 
