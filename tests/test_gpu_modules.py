@@ -145,6 +145,12 @@ def test_filip_process_batch_matches_oracle():
         if q.grad is not None and q.grad.abs().max() > 0:
             assert p.grad is not None and rel(p.grad, q.grad) <= 5e-4, (n, rel(p.grad, q.grad))
     assert abs(tf.evaluate(model, [batch], tok, DEV) - float(lo_val)) <= 1e-5 * abs(float(lo_val))
+    # the FILIP similarity figure's matrix = (simA + simB) / 2 (ref: modules/visualizations.py:54-73)
+    from modules import visualizations as vis
+    model.eval()
+    with torch.no_grad():
+        avg = vis._compute_embedding_cosine_similarities_filip(model, tok(batch[0]).to(DEV), tok(batch[1]).to(DEV))
+    assert rel(avg, (simA + simB) / 2) <= 1e-5
     assert float(tf._contrastive_loss(rA.detach(), use_dcl=True)) == pytest.approx(
         float(R.filip_contrastive_loss(rA.detach().cpu(), use_dcl=True)), rel=1e-5)
 
