@@ -427,6 +427,81 @@ class ClipSmall:
                              "the step is the launch + autograd overhead of 7 kernels"}}
 
 
+class EncoderHead:
+    """the encoder head behind a (stand-in) ESM trunk in evaluation mode -- projection 640 -> 128,
+    per-residue FFN, masked mean, pooled FFN, normalise, temperature (ref: modules/models.py:46-51) -- at the scripts'
+    sub-batch (16 sequences, depth 2 / 2) padded to 512 residues with PDB-like lengths: the fused two-launch path
+    (pclip_encoder_head_fwd) beside the stock nn.Sequential path on the same GPU and the oracle on the host cores."""
+    name = "encoder_head_b16"
+
+    def __init__(self, dist: Dist, Bs=16, T=512, Din=640):
+        import types
+        from modules import models
+        from pclip import ops, synth
+        self.ops, self.dev, self.Bs, self.T, self.Din = ops, dist.dev, Bs, T, Din
+        g = torch.Generator().manual_seed(synth.SEED + 8)
+        hidden = torch.randn(Bs, T, Din, generator=g)
+        lens = torch.clamp(synth.receptor_lengths(Bs, g, cap=2000) + 2, max=T)
+        self.cpu = (hidden, synth.prefix_mask(lens, T), torch.tensor(1.0))
+        self.h_hidden = hidden.pin_memory()
+        self.hidden, self.mask, self.tau = hidden.to(dist.dev), self.cpu[1].to(dist.dev), self.cpu[2].to(dist.dev)
+
+        class Trunk(torch.nn.Module):
+            def forward(s, input_ids=None, attention_mask=None):
+                return types.SimpleNamespace(last_hidden_state=self.cur)
+        torch.manual_seed(synth.SEED + 8)
+        self.enc = models.Encoder(Din, 128, 2, 2, 0.1, Trunk()).to(dist.dev).eval()
+        self.sd = {k: v.detach().cpu() for k, v in self.enc.state_dict().items()}
+        self.cur = self.hidden
+        self.host_out = torch.empty(Bs, 128).pin_memory()
+
+    def _seq(self):
+        return {"input_ids": self.mask, "attention_mask": self.mask, "temperature": self.tau}
+
+    def step(self):
+        with torch.no_grad():
+            return self.enc(self._seq())
+
+    def e2e_step(self):
+        self.cur = self.h_hidden.to(self.dev, non_blocking=True)
+        self.host_out.copy_(self.step(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        self.cur = self.hidden
+
+    def report(self, dist, steps=100, warmup=10):
+        from oracle import restate as R
+        self.ops.reset_launch_count()
+        ms = timed(dist, self.step, steps, warmup) / steps
+        launches = self.ops.launch_count() / (steps + warmup)
+        os.environ["PCLIP_FUSED_HEAD"] = "0"
+        try:
+            ms_stock = timed(dist, self.step, steps, warmup) / steps
+            stock = self.step()
+        finally:
+            del os.environ["PCLIP_FUSED_HEAD"]
+        fused = self.step()
+        ms_e = timed(dist, self.e2e_step, steps, warmup) / steps
+        want = R.encoder_head(self.cpu[0].double(), self.cpu[1], {k: v.double() for k, v in self.sd.items()},
+                              self.cpu[2].double())
+        t = cpu_time(lambda: R.encoder_head(self.cpu[0], self.cpu[1], self.sd, self.cpu[2]), reps=5)
+        err = lambda o: float((o.double().cpu() - want).abs().max() / want.abs().max())   # noqa: E731
+        n_res = int(self.cpu[1].sum())
+        flop = 2.0 * self.Bs * self.T * 128 * (self.Din + 2 * 128)
+        return {"us_per_step": round(ms * 1e3, 2), "sequences_per_s": round(self.Bs / (ms * 1e-3), 1), "dtype": "f32",
+                "shape": {"sequences": self.Bs, "padded_residues": self.T, "valid_residues": n_res, "Din": self.Din},
+                "pclip_launches_per_step": launches,
+                "stock_torch_path_same_gpu_us": round(ms_stock * 1e3, 2),
+                "check": {"fused_vs_float64_oracle": err(fused), "stock_vs_float64_oracle": err(stock)},
+                "e2e": e2e_block(self.Bs / (ms_e * 1e-3), "sequences/s", self.h_hidden.numel() * 4, self.Bs * 128 * 4, ms_e),
+                "cpu_baseline": {"value": round(self.Bs / t, 1), "unit": "sequences/s", "cores": torch.get_num_threads(),
+                                 "kind": "port", "sample": f"oracle/restate.py encoder_head, fp32, full size, best of 5: "
+                                 f"{t * 1e3:.2f} ms"},
+                "roofline": {"bound": "hbm", "achieved": round(self.hidden.numel() * 4 / (ms * 1e-3) / 1e9, 1),
+                             "unit": "GB/s", "note": f"reads the {self.hidden.numel() * 4 / 1e6:.0f} MB of hidden states once; "
+                             f"{flop / 1e9:.2f} GFLOP fp32 on the CUDA cores ({flop / (ms * 1e-3) / 1e12:.1f} TFLOP/s); at 16 "
+                             "sequences the grid is 256 CTAs of which the all-pad ones exit at once"}}
+
+
 class ClipGradCache:
     """configs[1]: _contrastive_loss_gc on 16 + 16 GradCache leaves of [16, 128] with grad_output = 65536
     (ref: modules/training_utils.py:137-139, :247-265), through the autograd entry point a user calls."""
@@ -908,6 +983,7 @@ def main():
         del w.plan, w.job
         torch.cuda.empty_cache()
         extras["clip_b16"] = extra("clip_b16", lambda: ClipSmall(dist), lambda wl: wl.report(dist))
+        extras["encoder_head_b16"] = extra("encoder_head_b16", lambda: EncoderHead(dist), lambda wl: wl.report(dist))
         extras["clip_gc256"] = extra("clip_gc256", lambda: ClipGradCache(dist), lambda wl: wl.report(dist))
         extras["filip_b256"] = extra("filip_b256", lambda: FilipB256(dist), lambda wl: wl.report(dist, peaks))
         extras["filip_b256_ragged"] = extra("filip_b256_ragged", lambda: FilipB256(dist, ragged=True),

@@ -272,6 +272,30 @@ int pclip_rowwise_infonce(const float* logits, int64_t B, int64_t Bc, int64_t di
                           void* workspace /* pclip_rowsum_workspace_bytes(B) */, size_t workspace_bytes,
                           pclip_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Fused encoder head, forward (ref: modules/models.py:46-51 Encoder.forward after the ESM trunk, and
+ * :192-196 FILIPEncoder.forward): projection Din -> E, per-residue FFN, then
+ *   out_tokens != NULL : the per-residue embeddings [Bs, T, E]                               (FILIPEncoder)
+ *   out_pooled != NULL : masked mean over residues (count clamped to >= 1, :75-90), pooled FFN, F.normalize(eps),
+ *                        * exp(tau / 2) -> [Bs, E]                                           (Encoder)
+ * Inference only: no dropout, nothing kept for a backward.  fp32, E = 128, Din % 4 == 0.  An FFN of depth h is h - 1
+ * layers with a LayerNorm (Linear, ReLU, LayerNorm: ln_weight / ln_bias set) followed by one plain Linear (both NULL),
+ * i.e. the nn.Sequential of models.py:66-73 in order.  All parameter pointers 16-byte aligned.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  const float* weight;    /* [E, K] row-major (nn.Linear.weight) */
+  const float* bias;      /* [E] */
+  const float* ln_weight; /* [E] LayerNorm weight, or NULL: no ReLU + LayerNorm after this Linear */
+  const float* ln_bias;   /* [E] */
+} pclip_linear_t;
+size_t pclip_encoder_head_workspace_bytes(int64_t Bs, int64_t T);   /* pooled mode only */
+int pclip_encoder_head_fwd(const float* hidden /* [Bs,T,Din] */, const int64_t* mask /* [Bs,T] 0/1 */, int64_t Bs, int64_t T,
+                           int32_t Din, int32_t E, const pclip_linear_t* projection /* HOST, 1 */,
+                           const pclip_linear_t* token_ffn /* HOST */, int32_t n_token,
+                           const pclip_linear_t* pooled_ffn /* HOST */, int32_t n_pooled, const float* tau /* [1] or NULL */,
+                           float ln_eps, float norm_eps, float* out_tokens, float* out_pooled, void* workspace,
+                           size_t workspace_bytes, pclip_stream_t stream);
+
 /* pclip_rowwise_infonce for callers that cannot allocate or own a workspace (CUDA graph capture, serving loops):
  * same arguments, arithmetic, summation order and results, but the scratch of the ordered loss sum lives in a
  * file-scope static __device__ array of the library (16.6 KB, held by every GPU that loads the library until exit).

@@ -192,6 +192,32 @@ def filip_cases(ref):
     _save("masked_mean", t=t, mask=m, out=FIL._masked_mean(t, m, dim=1))
 
 
+def encoder_head_case(ref):
+    """models.Encoder.forward and models.FILIPEncoder.forward end to end behind a fake ESM (eval mode): the whole head,
+    SURVEY.md 8(f)2.  Depths 3 / 2 so that more than one LayerNorm block is exercised; one all-pad sample (count
+    clamp), one non-prefix mask."""
+    torch.manual_seed(11)
+    B, T, Din, D = 5, 45, 40, 128
+    hidden = torch.randn(B, T, Din)
+    mask = synth.prefix_mask(torch.tensor([45, 33, 0, 7, 20]), T)
+    mask[4, 3] = 0
+    mask[4, 30] = 1
+    tau = torch.tensor(0.8)
+    enc = ref.models.Encoder(Din, D, 3, 2, 0.1, _FakeEsm(hidden)).eval()
+    for p in enc.parameters():          # LayerNorm weights / biases away from their 1 / 0 initialisation
+        if p.dim() == 1:
+            p.data.add_(0.1 * torch.randn_like(p))
+    fil = ref.models.FILIPEncoder(Din, D, 3, 2, 0.1, _FakeEsm(hidden)).eval()
+    fil.load_state_dict(enc.state_dict())
+    ids = torch.zeros(B, T, dtype=torch.long)
+    with torch.no_grad():
+        pooled = enc({"input_ids": ids, "attention_mask": mask, "temperature": tau})
+        tokens, m2 = fil({"input_ids": ids, "attention_mask": mask, "temperature": tau})
+    assert torch.equal(m2, mask)
+    sd = {"sd/" + k: v for k, v in enc.state_dict().items() if not k.startswith("esm_model")}
+    _save("encoder_head", hidden=hidden, mask=mask, tau=tau, pooled=pooled, tokens=tokens, **sd)
+
+
 def main():
     ref = ref_loader.load()
     torch.set_num_threads(1)  # fixed summation order for the fixtures
@@ -201,6 +227,7 @@ def main():
     rank_case(ref)
     cosine_case(ref)
     filip_cases(ref)
+    encoder_head_case(ref)
 
 
 if __name__ == "__main__":

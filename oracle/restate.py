@@ -243,6 +243,31 @@ def filip_loss_and_grads(hA_raw, hB_raw, maskA, maskB, tau, normalize: bool = Tr
                 argA=argA, argB=argB)
 
 
+# ---------------------------------------------------------------------------------------------------------
+# encoder head after the ESM trunk
+# ---------------------------------------------------------------------------------------------------------
+def _ffn_apply(x, sd, name, ln_eps):
+    """The nn.Sequential of models.py:66-73 from its state_dict entries, dropout inactive: blocks `<name>.<i>.0` (Linear),
+    ReLU, `<name>.<i>.2` (LayerNorm), then the last plain Linear `<name>.<depth-1>`."""
+    i = 0
+    while f"{name}.{i}.0.weight" in sd:
+        x = torch.relu(x @ sd[f"{name}.{i}.0.weight"].t() + sd[f"{name}.{i}.0.bias"])
+        x = torch.nn.functional.layer_norm(x, (x.shape[-1],), sd[f"{name}.{i}.2.weight"], sd[f"{name}.{i}.2.bias"], ln_eps)
+        i += 1
+    return x @ sd[f"{name}.{i}.weight"].t() + sd[f"{name}.{i}.bias"]
+
+
+def encoder_head(hidden, mask, sd, tau=None, pooled: bool = True, ln_eps: float = 1e-5):
+    """Encoder.forward after the trunk (ref: modules/models.py:46-51; masked mean :75-90) when pooled, else
+    FILIPEncoder.forward (:192-196).  `sd`: the encoder's state_dict (projection.*, amino_acid_ffn.*, embedding_ffn.*)."""
+    h = _ffn_apply(hidden @ sd["projection.weight"].t() + sd["projection.bias"], sd, "amino_acid_ffn", ln_eps)
+    if not pooled:
+        return h
+    mean = (h * mask.unsqueeze(-1)).sum(1) / mask.sum(1, keepdim=True).clamp(min=1)
+    e = _ffn_apply(mean, sd, "embedding_ffn", ln_eps)
+    return torch.nn.functional.normalize(e, dim=-1) * torch.exp(torch.as_tensor(tau) / 2)
+
+
 def bf16_round(t: torch.Tensor) -> torch.Tensor:
     """Round-to-nearest-even to bfloat16 and back (what the tensor-core path feeds the MMA)."""
     return t.to(torch.float32).to(torch.bfloat16).to(t.dtype)

@@ -15,6 +15,8 @@ PyTorch.  There is no CPU fallback: on CPU tensors 
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -65,6 +67,23 @@ class _Trunk(nn.Module):
                 seq["_esm_hidden"] = hidden.detach()
         return self.amino_acid_ffn(self.projection(hidden))
 
+    def _hidden(self, seq):
+        """ESM hidden states of `seq` (the cached ones during a GradCache replay, see _residues)."""
+        hidden = seq.get("_esm_hidden") if hasattr(seq, "get") else None
+        if hidden is None:
+            hidden = self.esm_model(input_ids=seq["input_ids"], attention_mask=seq["attention_mask"]).last_hidden_state
+        return hidden
+
+    def _fused_head_ok(self, pooled_ffn):
+        """Inference (eval mode, no autograd graph wanted): the whole head runs as two fused launches
+        (pclip.ops.encoder_head).  Training keeps the stock modules: their backward is autograd's.
+        Under autocast the reference's Linears run in half precision; the fused head computes them in fp32."""
+        if os.environ.get("PCLIP_FUSED_HEAD", "1") == "0" or torch.is_grad_enabled() or self.training:
+            return False      # (training mode even without grad: GradCache's first pass must equal its replay)
+        return self.projection.weight.is_cuda and ops.encoder_head_supported(
+            torch.empty(0, self.projection.in_features, device=self.projection.weight.device), self.projection,
+            self.amino_acid_ffn, pooled_ffn)
+
 
 class Encoder(_Trunk):
     """Sequence encoder of ExtendedCLIP.  forward(seq) with seq = {'input_ids', 'attention_mask', 'temperature'} returns
@@ -75,6 +94,9 @@ class Encoder(_Trunk):
 
     def forward(self, seq):
         mask = seq["attention_mask"]
+        if self._fused_head_ok(self.embedding_ffn):
+            return ops.encoder_head(self._hidden(seq), mask, self.projection, self.amino_acid_ffn, self.embedding_ffn,
+                                    seq["temperature"], norm_eps=1e-12)
         pooled = self._masked_mean(self._residues(seq), mask)
         return ops.normalize_scale(self.embedding_ffn(pooled), seq["temperature"], eps=1e-12)
 
@@ -108,6 +130,9 @@ class FILIPEncoder(_Trunk):
         super().__init__(input_dim, embedding_dim, h1, h2, dropout_rate, esm_model)
 
     def forward(self, seq):
+        if self._fused_head_ok(None):
+            return ops.encoder_head(self._hidden(seq), seq["attention_mask"], self.projection,
+                                    self.amino_acid_ffn), seq["attention_mask"]
         return self._residues(seq), seq["attention_mask"]
 
 

@@ -28,6 +28,10 @@ class Chunk(C.Structure):
     _fields_ = [("ptr", C.c_void_p), ("rows", C.c_int64), ("row_stride", C.c_int64), ("col_stride", C.c_int64)]
 
 
+class Linear(C.Structure):   # pclip_linear_t
+    _fields_ = [("weight", C.c_void_p), ("bias", C.c_void_p), ("ln_weight", C.c_void_p), ("ln_bias", C.c_void_p)]
+
+
 class FwdSide(C.Structure):
     _fields_ = [("a", C.c_void_p), ("b", C.c_void_p), ("Ma", C.c_int64), ("Nb", C.c_int64),
                 ("diag_offset", C.c_int64), ("rowsum", C.c_void_p), ("diag", C.c_void_p)]
@@ -83,6 +87,9 @@ SIGNATURES = {
     "pclip_filip_fwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _I32, _P, _P, _P, _P, _P, _SZ, _P]),
     "pclip_filip_bwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P,
                                   _P, _P, _SZ, _P]),
+    "pclip_encoder_head_workspace_bytes": (_SZ, [_I64, _I64]),
+    "pclip_encoder_head_fwd": (C.c_int, [_P, _P, _I64, _I64, _I32, _I32, C.POINTER(Linear), C.POINTER(Linear), _I32,
+                                         C.POINTER(Linear), _I32, _P, _F, _F, _P, _P, _P, _SZ, _P]),
     "pclip_rowwise_infonce_noalloc_max_rows": (_I64, []),
     "pclip_rowwise_infonce_noalloc": (C.c_int, [_P, _I64, _I64, _I64, _F, _P, _P, _P]),
     "pclip_rowwise_infonce": (C.c_int, [_P, _I64, _I64, _I64, _F, _P, _P, _P, _SZ, _P]),

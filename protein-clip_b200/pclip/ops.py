@@ -669,3 +669,88 @@ def rowwise_infonce(logits: torch.Tensor, weight: float = 1.0, diag_offset: int 
 def filip_loss(simA: torch.Tensor, simB: torch.Tensor, diag_offset: int = 0) -> torch.Tensor:
     """(loss_A + loss_B) / 2 with BOTH matrices normalised row-wise (ref: training_utils_filip.py:26-39)."""
     return rowwise_infonce(simA, 0.5, diag_offset) + rowwise_infonce(simB, 0.5, diag_offset)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# (5) fused encoder head, forward (SURVEY.md 8(f)2)      ref: modules/models.py:46-51 and :192-196
+# ---------------------------------------------------------------------------------------------------------
+def _ffn_layers(ffn):
+    """nn.Sequential built by _build_ffn (ref: modules/models.py:66-73) -> list of (Linear, LayerNorm | None), or None
+    when the module does not have that shape (then the caller keeps the stock path)."""
+    out = []
+    mods = list(ffn)
+    for i, m in enumerate(mods):
+        if isinstance(m, torch.nn.Linear) and i == len(mods) - 1:
+            out.append((m, None))
+        elif isinstance(m, torch.nn.Sequential) and len(m) == 4 and isinstance(m[0], torch.nn.Linear) and \
+                isinstance(m[1], torch.nn.ReLU) and isinstance(m[2], torch.nn.LayerNorm) and \
+                isinstance(m[3], torch.nn.Dropout) and m[2].elementwise_affine and m[2].bias is not None:
+            out.append((m[0], m[2]))
+        else:
+            return None
+    return out
+
+
+def _linear_array(layers, keep):
+    arr = (L.Linear * max(len(layers), 1))()
+    for i, (lin, ln) in enumerate(layers):
+        ts = [lin.weight, lin.bias, ln.weight if ln is not None else None, ln.bias if ln is not None else None]
+        ts = [None if t is None else t.detach().float().contiguous() for t in ts]
+        keep.extend(ts)
+        arr[i] = L.Linear(*[L.ptr(t) for t in ts])
+    return arr
+
+
+def encoder_head_supported(hidden, projection, token_ffn, pooled_ffn) -> bool:
+    """True when the fused kernels cover this head: CUDA fp32 parameters, width 128, Din % 4 == 0, FFNs of the reference's
+    shape with at most 8 layers, biases present, one LayerNorm eps."""
+    if not (hidden.is_cuda and projection.weight.is_cuda and projection.bias is not None):
+        return False
+    if projection.out_features != 128 or projection.in_features % 4 or hidden.shape[-1] != projection.in_features:
+        return False
+    eps = set()
+    for ffn in (token_ffn, pooled_ffn):
+        if ffn is None:
+            continue
+        layers = _ffn_layers(ffn)
+        if layers is None or len(layers) > 8:
+            return False
+        for lin, ln in layers:
+            if lin.in_features != 128 or lin.out_features != 128 or lin.bias is None or lin.weight.dtype != torch.float32:
+                return False
+            if ln is not None:
+                eps.add(ln.eps)
+    return len(eps) <= 1 and projection.weight.dtype == torch.float32
+
+
+def encoder_head(hidden, mask, projection, token_ffn, pooled_ffn=None, tau=None, norm_eps: float = 1e-12):
+    """hidden [Bs, T, Din] (the ESM trunk's last_hidden_state), mask [Bs, T].  pooled_ffn None: per-residue embeddings
+    [Bs, T, 128] (FILIPEncoder); else F.normalize(pooled_ffn(masked_mean(...))) * exp(tau / 2) [Bs, 128] (Encoder).
+    Inference only (no autograd graph is recorded)."""
+    L.require_cuda(hidden, mask)
+    dev = hidden.device
+    hid = hidden.detach().float().contiguous()
+    m = mask.detach().to(torch.int64).contiguous()
+    Bs, T, Din = hid.shape
+    keep = []
+    tok_layers = _ffn_layers(token_ffn)
+    proj = _linear_array([(projection, None)], keep)
+    tok = _linear_array(tok_layers, keep)
+    pooled = pooled_ffn is not None
+    pl_layers = _ffn_layers(pooled_ffn) if pooled else []
+    pl = _linear_array(pl_layers, keep)
+    lns = [ln for _, ln in tok_layers + pl_layers if ln is not None]
+    ln_eps = float(lns[0].eps) if lns else 1e-5
+    out = torch.empty((Bs, 128) if pooled else (Bs, T, 128), dtype=torch.float32, device=dev)
+    if Bs == 0:
+        return out
+    t = None if tau is None else torch.as_tensor(tau).detach().float().reshape(1).to(dev)
+    lib = L.lib()
+    with torch.cuda.device(dev):
+        n = int(lib.pclip_encoder_head_workspace_bytes(Bs, T)) if pooled else 0
+        owner, ws = L.workspace(n, dev) if pooled else (None, None)
+        L.check(lib.pclip_encoder_head_fwd(L.ptr(hid), L.ptr(m), Bs, T, Din, 128, proj, tok, len(tok_layers), pl,
+                                           len(pl_layers), L.ptr(t), ln_eps, float(norm_eps),
+                                           None if pooled else L.ptr(out), L.ptr(out) if pooled else None, ws, n,
+                                           L.stream_ptr(dev)))
+    return out

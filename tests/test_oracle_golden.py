@@ -117,3 +117,12 @@ def test_untrained_loss_is_ln_b():
     # soft anchor from the reference's notebooks/filip.ipynb cell 19: -log(1/16) = 2.7725887
     z = torch.zeros(16, 128, dtype=F64)
     assert abs(float(R.clip_loss(z, z.t())) - np.log(16)) < 1e-12
+
+
+def test_encoder_head(golden):
+    """The restated head (projection, per-residue FFN, masked mean, pooled FFN, normalise, temperature) against the
+    reference's own Encoder / FILIPEncoder forward behind a fake ESM (eval mode), SURVEY.md 8(f)2."""
+    g = golden("encoder_head", F64)
+    sd = {k[3:]: v for k, v in g.items() if k.startswith("sd/")}
+    close(R.encoder_head(g["hidden"], g["mask"], sd, g["tau"], pooled=True), g["pooled"])
+    close(R.encoder_head(g["hidden"], g["mask"], sd, pooled=False), g["tokens"])
