@@ -300,6 +300,12 @@ int filip_gather_side(const __nv_bfloat16* Yr, const int32_t* lenX, const int32_
                       const float* gY, int64_t gy0, int64_t gy1, const int16_t* argX, const int16_t* argY, float2* w2,
                       uint32_t* inv, uint32_t* grp2, float* dX, cudaStream_t st);
 
+// filip_tc1.cu
+int tc_filip_both_fwd(const __nv_bfloat16* X, const __nv_bfloat16* Y, const int32_t* lenX, const int32_t* lenY, int64_t Bx,
+                      int64_t By, int64_t Tx, int64_t Ty, const float* tau, float* partX, int npX, int16_t* argX,
+                      float* partY, int16_t* argY, float* outX, int64_t sx0, int64_t sx1, float* outY, int64_t sy0,
+                      int64_t sy1, cudaStream_t st);
+
 struct FilipWs {
   __nv_bfloat16 *Ar, *Br;
   float *pa, *pb;        // forward: per-warp partial sums of the masked means
@@ -385,6 +391,18 @@ int tc_filip_fwd(const float* hA, const float* hB, const int32_t* lenA, const in
   PCLIP_REQUIRE(f.ok, PCLIP_ERR_WORKSPACE, "filip_fwd: workspace too small");
   PCLIP_TRY(filip_prep(hA, lenA, Ba, TA, f.Ar, st));
   PCLIP_TRY(filip_prep(hB, lenB, Bb, TB, f.Br, st));
+  // One sweep for both sides (filip_tc1.cu) when one modality's samples fit a CTA's 4 stationary row tiles; otherwise
+  // (or with PCLIP_FILIP_FWD=2, for A/B runs) one launch per side.
+  static const int mode = [] {
+    const char* e = getenv("PCLIP_FILIP_FWD");
+    return e ? atoi(e) : 0;
+  }();
+  if (mode != 2 && TA <= 512)
+    return tc_filip_both_fwd(f.Ar, f.Br, lenA, lenB, Ba, Bb, TA, TB, tau, f.pa, np_of(TA), argA, f.pb, argB, simA, Bb, 1,
+                             simB, 1, Bb, st);
+  if (mode != 2 && TB <= 512)
+    return tc_filip_both_fwd(f.Br, f.Ar, lenB, lenA, Bb, Ba, TB, TA, tau, f.pb, np_of(TB), argB, f.pa, argA, simB, 1, Bb,
+                             simA, Bb, 1, st);
   PCLIP_TRY(tc_side_fwd(f.Ar, f.Br, lenA, lenB, Ba, Bb, TA, TB, tau, f.pa, argA, simA, Bb, 1, st));
   PCLIP_TRY(tc_side_fwd(f.Br, f.Ar, lenB, lenA, Bb, Ba, TB, TA, tau, f.pb, argB, simB, 1, Bb, st));
   return PCLIP_OK;
