@@ -38,7 +38,10 @@ constexpr int kStages = 2;                     // column-tile ring (each tile fe
 constexpr int kThreads = 32 * (2 + 4 * kMaxH + 1);   // TMA warp, MMA warp, 4 epilogue warps per row tile, column finaliser
 constexpr int kSlots = kMaxH * 4;              // (row tile, lane quarter) writers per column tile
 constexpr uint32_t kColBufBytes = 2 * kSlots * kTile * 4;
-constexpr uint32_t kSmem = kTileBytes * (kMaxH + kStages) + kColBufBytes + 256 + 1024;
+constexpr int kScratchStride = 35;             // words per g row of a warp's transposition patch (32 columns + pad)
+constexpr uint32_t kScratchBytes = 4 * kMaxH * 8 * kScratchStride * 4;
+constexpr uint32_t kSmem = kTileBytes * (kMaxH + kStages) + kColBufBytes + kScratchBytes + 256 + 1024;
+static_assert(kSmem <= 232448, "shared memory");
 constexpr uint32_t kNegKey = 0xff7fffe0u;      // key of -FLT_MAX
 constexpr uint32_t kNegMax = 0xff7fffffu;      // -FLT_MAX
 
@@ -88,7 +91,7 @@ __device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(
 
 struct RowState {
   uint32_t mk[4];   // running maximum of row g + 8j over this lane's columns, as a key
-  int base[4];      // first column of the 32-column chunk it came from
+  int base[4];      // first column of the tile it came from
 };
 
 __device__ __forceinline__ void reset(RowState& s) {
@@ -99,11 +102,34 @@ __device__ __forceinline__ void reset(RowState& s) {
   }
 }
 
-// One 32 x 32 chunk.  nv = valid columns of the chunk (>= 1; < 32 only in a column sample's last tile), rowmask: bit j
-// set = row g + 8j is a pad row (excluded from the column maxima).  Returns the column winner this lane ends up with:
-// column 8 (g >> 1) + 2c + (g & 1) of the chunk, low 5 bits = 31 - (winning row within the warp's 32).
-__device__ __forceinline__ uint32_t chunk_both(uint32_t (&r)[32], const int col0, const int nv, const uint32_t rowmask,
-                                               const int lane, RowState& st) {
+// column candidates of the 8 lane groups g: (candidate & ~7) | (7 - g), ONE LOP3 each
+template <int G>
+__device__ __forceinline__ void tag_rows(const uint32_t* col, const uint32_t gkeep, float (&w)[8]) {
+  if constexpr (G < 8) {
+    uint32_t v;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(v) : "r"(col[G * kScratchStride]), "r"(gkeep), "n"(7 - G));
+    w[G] = __uint_as_float(v);
+    tag_rows<G + 1>(col, gkeep, w);
+  }
+}
+
+// After a tile's chunks: the tile's row winners against the running maxima (an earlier tile keeps a tie).
+__device__ __forceinline__ void tile_rows(const float (&rowwin)[4], const int s0, RowState& st) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t m = __float_as_uint(rowwin[j]);
+    if (__uint_as_float(m | 31u) > __uint_as_float(st.mk[j] | 31u)) {
+      st.mk[j] = m;
+      st.base[j] = s0;
+    }
+  }
+}
+
+// One 32 x 32 chunk (chunk cc of its tile).  nv = valid columns of the chunk (>= 1; < 32 only in a column sample's last tile), rowmask: bit j
+// set = row g + 8j is a pad row (excluded from the column maxima).  Returns the winner of column `lane` of the chunk,
+// low 5 bits = 31 - (winning row within the warp's 32).
+__device__ __forceinline__ uint32_t chunk_both(uint32_t (&r)[32], const int cc, const int nv, const uint32_t rowmask,
+                                               const int lane, float (&rowwin)[4], uint32_t* scratch) {
   const int c = lane & 3;
   if (nv < 32) {
 #pragma unroll
@@ -119,16 +145,18 @@ __device__ __forceinline__ uint32_t chunk_both(uint32_t (&r)[32], const int col0
   uint32_t keep;   // in a register the optimiser cannot see through: (r & keep) | imm is then ONE LOP3
   asm("mov.u32 %0, 0xffffffe0;" : "=r"(keep));
   make_keys<0>(r, keep, key);
-  // row direction
+  // row direction: 8 keys -> 1; the j bits (constant within a row) are replaced by 3 - (chunk within the tile), so the
+  // chunk winners of a tile combine by plain maxima and the running maximum is updated once per tile (tile_rows)
+  uint32_t cmask, ccode = (uint32_t)(3 - cc) << 3;
+  asm("mov.u32 %0, 0xffffffe7;" : "=r"(cmask));
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const float a = max3(key[reg_of(j, 0, 0)], key[reg_of(j, 0, 1)], key[reg_of(j, 1, 0)]);
     const float b = max3(key[reg_of(j, 1, 1)], key[reg_of(j, 2, 0)], key[reg_of(j, 2, 1)]);
     const uint32_t m = __float_as_uint(max3(a, b, fmaxf(key[reg_of(j, 3, 0)], key[reg_of(j, 3, 1)])));
-    if (__uint_as_float(m | 31u) > __uint_as_float(st.mk[j] | 31u)) {   // an earlier chunk keeps a tie
-      st.mk[j] = m;
-      st.base[j] = col0;
-    }
+    uint32_t v;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(v) : "r"(m), "r"(cmask), "r"(ccode));
+    rowwin[j] = cc == 0 ? __uint_as_float(v) : fmaxf(rowwin[j], __uint_as_float(v));
   }
   // column direction: pad rows out, 4 rows -> 1 in-thread, row-in-warp code, butterfly over g
   if (rowmask) {
@@ -141,33 +169,25 @@ __device__ __forceinline__ uint32_t chunk_both(uint32_t (&r)[32], const int col0
           for (int e = 0; e < 2; ++e) key[reg_of(j, k, e)] = __uint_as_float(kNegKey);
       }
   }
-  uint32_t gkeep, gcode = 7u - (uint32_t)(lane >> 2);
-  asm("mov.u32 %0, 0xfffffff8;" : "=r"(gkeep));
-  float w[8];
+  // 4 rows -> 1 in-thread, then the 8 lanes (g) that share a column set meet through a warp-private shared-memory
+  // patch [g][column] (row stride 35 words): lane L reads column L's 8 candidates, tags each with 7 - g in the 3 bits
+  // the column index no longer needs, and reduces them with one FMNMX3 tree.  (The first version exchanged them
+  // with a transposing shuffle butterfly: 8 LOP3 + 14 SEL + 7 FMNMX on the ALU pipe that bounds this kernel
+  // instead of 8 LOP3 + 4 FMNMX.)
+  uint32_t* mine = scratch + (lane >> 2) * kScratchStride + 2 * c;
 #pragma unroll
   for (int k = 0; k < 4; ++k)
 #pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const float m = max3(key[reg_of(0, k, e)], key[reg_of(1, k, e)],
-                           fmaxf(key[reg_of(2, k, e)], key[reg_of(3, k, e)]));
-      uint32_t v;
-      asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(v) : "r"(__float_as_uint(m)), "r"(gkeep), "r"(gcode));
-      w[2 * k + e] = __uint_as_float(v);
-    }
-  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
-  float x[4], y[2];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float keepv = b4 ? w[i + 4] : w[i], send = b4 ? w[i] : w[i + 4];
-    x[i] = fmaxf(keepv, __shfl_xor_sync(0xffffffffu, send, 16));
-  }
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const float keepv = b3 ? x[i + 2] : x[i], send = b3 ? x[i] : x[i + 2];
-    y[i] = fmaxf(keepv, __shfl_xor_sync(0xffffffffu, send, 8));
-  }
-  const float keepv = b2 ? y[1] : y[0], send = b2 ? y[0] : y[1];
-  return __float_as_uint(fmaxf(keepv, __shfl_xor_sync(0xffffffffu, send, 4)));
+    for (int e = 0; e < 2; ++e)
+      mine[8 * k + e] = __float_as_uint(max3(key[reg_of(0, k, e)], key[reg_of(1, k, e)],
+                                             fmaxf(key[reg_of(2, k, e)], key[reg_of(3, k, e)])));
+  __syncwarp();
+  uint32_t gkeep;
+  asm("mov.u32 %0, 0xfffffff8;" : "=r"(gkeep));
+  float w[8];
+  tag_rows<0>(scratch + lane, gkeep, w);
+  __syncwarp();
+  return __float_as_uint(max3(max3(w[0], w[1], w[2]), max3(w[3], w[4], w[5]), fmaxf(w[6], w[7])));
 }
 }  // namespace f1
 
@@ -199,7 +219,8 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
   uint8_t* a_tiles = smem;
   uint8_t* b_tiles = a_tiles + kMaxH * kTileBytes;
   uint32_t* colbuf = reinterpret_cast<uint32_t*>(b_tiles + kStages * kTileBytes);   // [2][kSlots][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(colbuf) + kColBufBytes);
+  uint32_t* scratch_all = colbuf + kColBufBytes / 4;                                 // [16 warps][8][kScratchStride]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(scratch_all) + kScratchBytes);
   uint64_t* a_full = bars;
   uint64_t* b_full = a_full + 1;            // [kStages]
   uint64_t* b_empty = b_full + kStages;     // [kStages]
@@ -291,6 +312,7 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
     const int q = warp & 3, h = (warp - 2) >> 2;
     const int g = lane >> 2, c = lane & 3;
     const bool live = h < nh;
+    uint32_t* scratch = scratch_all + (warp - 2) * 8 * kScratchStride;
     RowState st;
     reset(st);
     uint32_t rowmask = 0u;
@@ -309,8 +331,9 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
           const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * kTile;
           const int nvalid = min(ly - s0, kTile);   // >= 1
           const int nb = ct & 1;
-          uint32_t* mine = colbuf + ((size_t)nb * kSlots + h * 4 + q) * kTile + 8 * (g >> 1) + 2 * c + (g & 1);
+          uint32_t* mine = colbuf + ((size_t)nb * kSlots + h * 4 + q) * kTile + lane;
           uint32_t ra[32];
+          float rowwin[4];
           if (nvalid == kTile) {
             uint32_t w[4];
 #pragma unroll
@@ -321,8 +344,9 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
                 tc_fence_before_sync();
                 mbar_arrive(&t_empty[buf]);
               }
-              w[cc] = kDbg ? ra[cc] : chunk_both(ra, s0 + cc * 32, 32, rowmask, lane, st);
+              w[cc] = kDbg ? ra[cc] : chunk_both(ra, cc, 32, rowmask, lane, rowwin, scratch);
             }
+            if (!kDbg) tile_rows(rowwin, s0, st);
             mbar_wait(&c_empty[nb], ((uint32_t)(ct >> 1) & 1u) ^ 1u);
 #pragma unroll
             for (int cc = 0; cc < 4; ++cc) mine[cc * 32] = w[cc];
@@ -332,8 +356,9 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
             for (int cc = 0; cc * 32 < nvalid; ++cc) {   // warp-uniform
               load_chunk(taddr + cc * 32, ra);
               tmem_ld_wait();
-              mine[cc * 32] = chunk_both(ra, s0 + cc * 32, min(nvalid - cc * 32, 32), rowmask, lane, st);
+              mine[cc * 32] = chunk_both(ra, cc, min(nvalid - cc * 32, 32), rowmask, lane, rowwin, scratch);
             }
+            tile_rows(rowwin, s0, st);
             tc_fence_before_sync();
             mbar_arrive(&t_empty[buf]);
           }
@@ -345,9 +370,9 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
       int col[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int v = 7 - (int)(st.mk[j] & 7u);
+        const int v = 7 - (int)(st.mk[j] & 7u), cc = 3 - (int)((st.mk[j] >> 3) & 3u);
         sb[j] = st.mk[j] | 31u;
-        col[j] = st.base[j] + 8 * (v >> 1) + 2 * c + (v & 1);
+        col[j] = st.base[j] + 32 * cc + 8 * (v >> 1) + 2 * c + (v & 1);
 #pragma unroll
         for (int o = 1; o <= 2; o <<= 1) {
           const uint32_t osb = __shfl_xor_sync(0xffffffffu, sb[j], o);
