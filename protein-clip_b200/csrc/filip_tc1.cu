@@ -38,8 +38,7 @@ constexpr int kStages = 2;                     // column-tile ring (each tile fe
 constexpr int kThreads = 32 * (2 + 4 * kMaxH + 1);   // TMA warp, MMA warp, 4 epilogue warps per row tile, column finaliser
 constexpr int kSlots = kMaxH * 4;              // (row tile, lane quarter) writers per column tile
 constexpr uint32_t kColBufBytes = 2 * kSlots * kTile * 4;
-constexpr int kScratchStride = 35;             // words per g row of a warp's transposition patch (32 columns + pad)
-constexpr uint32_t kScratchBytes = 4 * kMaxH * 8 * kScratchStride * 4;
+constexpr uint32_t kScratchBytes = 4 * kMaxH * 1024;   // one 32 x 8-word transposition patch per epilogue warp
 constexpr uint32_t kSmem = kTileBytes * (kMaxH + kStages) + kColBufBytes + kScratchBytes + 256 + 1024;
 static_assert(kSmem <= 232448, "shared memory");
 constexpr uint32_t kNegKey = 0xff7fffe0u;      // key of -FLT_MAX
@@ -102,17 +101,6 @@ __device__ __forceinline__ void reset(RowState& s) {
   }
 }
 
-// column candidates of the 8 lane groups g: (candidate & ~7) | (7 - g), ONE LOP3 each
-template <int G>
-__device__ __forceinline__ void tag_rows(const uint32_t* col, const uint32_t gkeep, float (&w)[8]) {
-  if constexpr (G < 8) {
-    uint32_t v;
-    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(v) : "r"(col[G * kScratchStride]), "r"(gkeep), "n"(7 - G));
-    w[G] = __uint_as_float(v);
-    tag_rows<G + 1>(col, gkeep, w);
-  }
-}
-
 // After a tile's chunks: the tile's row winners against the running maxima (an earlier tile keeps a tie).
 __device__ __forceinline__ void tile_rows(const float (&rowwin)[4], const int s0, RowState& st) {
 #pragma unroll
@@ -125,11 +113,18 @@ __device__ __forceinline__ void tile_rows(const float (&rowwin)[4], const int s0
   }
 }
 
+struct Patch {         // this lane's addresses in its warp's transposition patch
+  uint32_t* wr;        // word 8c + g
+  const uint4* rd0;    // slot `lane`, the half lanes with bit 2 clear read first
+  const uint4* rd1;
+  uint32_t gcode;      // 7 - g
+};
+
 // One 32 x 32 chunk (chunk cc of its tile).  nv = valid columns of the chunk (>= 1; < 32 only in a column sample's last tile), rowmask: bit j
-// set = row g + 8j is a pad row (excluded from the column maxima).  Returns the winner of column `lane` of the chunk,
-// low 5 bits = 31 - (winning row within the warp's 32).
+// set = row g + 8j is a pad row (excluded from the column maxima).  Returns the winner of column
+// 8 (lane >> 3) + 2 (lane & 3) + ((lane >> 2) & 1) of the chunk, low 5 bits = 31 - (winning row within the warp's 32).
 __device__ __forceinline__ uint32_t chunk_both(uint32_t (&r)[32], const int cc, const int nv, const uint32_t rowmask,
-                                               const int lane, float (&rowwin)[4], uint32_t* scratch) {
+                                               const int lane, float (&rowwin)[4], const Patch& pa) {
   const int c = lane & 3;
   if (nv < 32) {
 #pragma unroll
@@ -169,25 +164,29 @@ __device__ __forceinline__ uint32_t chunk_both(uint32_t (&r)[32], const int cc, 
           for (int e = 0; e < 2; ++e) key[reg_of(j, k, e)] = __uint_as_float(kNegKey);
       }
   }
-  // 4 rows -> 1 in-thread, then the 8 lanes (g) that share a column set meet through a warp-private shared-memory
-  // patch [g][column] (row stride 35 words): lane L reads column L's 8 candidates, tags each with 7 - g in the 3 bits
-  // the column index no longer needs, and reduces them with one FMNMX3 tree.  (The first version exchanged them
-  // with a transposing shuffle butterfly: 8 LOP3 + 14 SEL + 7 FMNMX on the ALU pipe that bounds this kernel
-  // instead of 8 LOP3 + 4 FMNMX.)
-  uint32_t* mine = scratch + (lane >> 2) * kScratchStride + 2 * c;
+  // 4 rows -> 1 in-thread, tagged with 7 - g in the 3 bits the column index no longer needs; then the 8 lanes (g) that
+  // share a column set meet through a warp-private shared-memory patch [column slot][g] (1 KB): slot = c | e << 2 |
+  // k << 3, so the 32 lanes of one store hit 32 banks (word 8c + g + 32e + 64k), and lane L reads slot L's 8
+  // candidates with two 16-byte loads (lanes with bit 2 set take the halves in the other order: no bank conflicts)
+  // and reduces them with one FMNMX3 tree.  (The first version exchanged the candidates with a transposing shuffle
+  // butterfly: 14 SEL + 7 FMNMX more on the ALU pipe that bounds this kernel.)
+  uint32_t gkeep;
+  asm("mov.u32 %0, 0xfffffff8;" : "=r"(gkeep));
 #pragma unroll
   for (int k = 0; k < 4; ++k)
 #pragma unroll
-    for (int e = 0; e < 2; ++e)
-      mine[8 * k + e] = __float_as_uint(max3(key[reg_of(0, k, e)], key[reg_of(1, k, e)],
-                                             fmaxf(key[reg_of(2, k, e)], key[reg_of(3, k, e)])));
+    for (int e = 0; e < 2; ++e) {
+      const float m = max3(key[reg_of(0, k, e)], key[reg_of(1, k, e)], fmaxf(key[reg_of(2, k, e)], key[reg_of(3, k, e)]));
+      uint32_t v;
+      asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(v) : "r"(__float_as_uint(m)), "r"(gkeep), "r"(pa.gcode));
+      pa.wr[32 * e + 64 * k] = v;
+    }
   __syncwarp();
-  uint32_t gkeep;
-  asm("mov.u32 %0, 0xfffffff8;" : "=r"(gkeep));
-  float w[8];
-  tag_rows<0>(scratch + lane, gkeep, w);
+  const uint4 a = *pa.rd0, b = *pa.rd1;
   __syncwarp();
-  return __float_as_uint(max3(max3(w[0], w[1], w[2]), max3(w[3], w[4], w[5]), fmaxf(w[6], w[7])));
+  return __float_as_uint(max3(max3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z)),
+                              max3(__uint_as_float(a.w), __uint_as_float(b.x), __uint_as_float(b.y)),
+                              fmaxf(__uint_as_float(b.z), __uint_as_float(b.w))));
 }
 }  // namespace f1
 
@@ -219,7 +218,7 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
   uint8_t* a_tiles = smem;
   uint8_t* b_tiles = a_tiles + kMaxH * kTileBytes;
   uint32_t* colbuf = reinterpret_cast<uint32_t*>(b_tiles + kStages * kTileBytes);   // [2][kSlots][128]
-  uint32_t* scratch_all = colbuf + kColBufBytes / 4;                                 // [16 warps][8][kScratchStride]
+  uint32_t* scratch_all = colbuf + kColBufBytes / 4;                                 // [16 warps][32 slots][8]
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(scratch_all) + kScratchBytes);
   uint64_t* a_full = bars;
   uint64_t* b_full = a_full + 1;            // [kStages]
@@ -312,7 +311,10 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
     const int q = warp & 3, h = (warp - 2) >> 2;
     const int g = lane >> 2, c = lane & 3;
     const bool live = h < nh;
-    uint32_t* scratch = scratch_all + (warp - 2) * 8 * kScratchStride;
+    uint32_t* scratch = scratch_all + (warp - 2) * 256;
+    const int hb = (lane >> 2) & 1;
+    const Patch pa{scratch + 8 * c + g, reinterpret_cast<const uint4*>(scratch + 8 * lane + 4 * hb),
+                   reinterpret_cast<const uint4*>(scratch + 8 * lane + 4 * (1 - hb)), 7u - (uint32_t)g};
     RowState st;
     reset(st);
     uint32_t rowmask = 0u;
@@ -331,7 +333,7 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
           const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * kTile;
           const int nvalid = min(ly - s0, kTile);   // >= 1
           const int nb = ct & 1;
-          uint32_t* mine = colbuf + ((size_t)nb * kSlots + h * 4 + q) * kTile + lane;
+          uint32_t* mine = colbuf + ((size_t)nb * kSlots + h * 4 + q) * kTile + 8 * (lane >> 3) + 2 * c + ((lane >> 2) & 1);
           uint32_t ra[32];
           float rowwin[4];
           if (nvalid == kTile) {
@@ -344,7 +346,7 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
                 tc_fence_before_sync();
                 mbar_arrive(&t_empty[buf]);
               }
-              w[cc] = kDbg ? ra[cc] : chunk_both(ra, cc, 32, rowmask, lane, rowwin, scratch);
+              w[cc] = kDbg ? ra[cc] : chunk_both(ra, cc, 32, rowmask, lane, rowwin, pa);
             }
             if (!kDbg) tile_rows(rowwin, s0, st);
             mbar_wait(&c_empty[nb], ((uint32_t)(ct >> 1) & 1u) ^ 1u);
@@ -356,7 +358,7 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
             for (int cc = 0; cc * 32 < nvalid; ++cc) {   // warp-uniform
               load_chunk(taddr + cc * 32, ra);
               tmem_ld_wait();
-              mine[cc * 32] = chunk_both(ra, cc, min(nvalid - cc * 32, 32), rowmask, lane, rowwin, scratch);
+              mine[cc * 32] = chunk_both(ra, cc, min(nvalid - cc * 32, 32), rowmask, lane, rowwin, pa);
             }
             tile_rows(rowwin, s0, st);
             tc_fence_before_sync();
