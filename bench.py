@@ -677,17 +677,18 @@ class FilipB256:
                 for i in range(3):
                     acc[i] += self.ev[i].elapsed_time(self.ev[i + 1]) / steps
             self.ev = None
-            out["split_ms"] = {"similarity_forward (2 x tc_filip_max_kernel + prep + finalize)": round(acc[0], 3),
+            out["split_ms"] = {"similarity_forward (tc_filip_both_kernel + prep + finalize)": round(acc[0], 3),
                                "loss_tail_forward": round(acc[1], 3),
                                "backward (loss tail, 2 x invert + gather, normalise)": round(acc[2], 3)}
             ach = flops / (acc[0] * 1e-3) / 1e12
-            tr, src = profile_traffic("tc_filip_max_kernel")
-            out["roofline"] = {"bound": "tensor", "kernel": "tc_filip_max_kernel (2 launches per step: one per side)",
+            tr, src = profile_traffic("tc_filip_both_kernel")
+            out["roofline"] = {"bound": "tensor", "kernel": "tc_filip_both_kernel (one sweep: row and column maxima of every tile)",
                                "achieved": round(ach, 1), "peak": peaks["tc"], "unit": "TFLOP/s",
                                "frac": round(ach / peaks["tc"], 4), "traffic": tr, "traffic_source": src,
                                "algorithmic_flops_per_step": flops, "kernel_ms": round(acc[0], 4),
-                               "note": "algorithmic = 2 sum(lenA lenB) D once; the two launches EXECUTE twice that "
-                                       "(S and S^T: in-thread row and column maxima), so 0.5 is this design's ceiling"}
+                               "note": "algorithmic = 2 sum(lenA lenB) D, executed once (the round-1/2 kernels computed S "
+                                       "and S^T); the MMA pipeline alone runs this sweep in 3.18 ms (power-limited "
+                                       "tensor rate), the epilogue's ALU work is what is left"}
         ms_e = timed(dist, self.e2e_step, steps, warmup) / steps
         bytes_in = (self.hostA.numel() + self.hostB.numel()) * 4 * (dist.world if self.job else 1)
         out["e2e"] = e2e_block(self.B / (ms_e * 1e-3), "pairs/s", bytes_in, 4 * (dist.world if self.job else 1), ms_e)

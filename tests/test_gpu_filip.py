@@ -78,10 +78,14 @@ def _oracle_on_rounded(hA, hB, maskA, maskB, tau):
                                   tau.double(), normalize=False)
 
 
-@pytest.mark.parametrize("B,TA,TB,ragged", [(3, 130, 257, True), (6, 512, 300, True), (4, 256, 256, False)])
+@pytest.mark.parametrize("B,TA,TB,ragged", [(3, 130, 257, True), (6, 512, 300, True), (4, 256, 256, False),
+                                            (2, 640, 200, True), (2, 33, 640, True), (2, 600, 520, True),
+                                            (3, 512, 512, False)])
 def test_filip_bf16_vs_oracle_on_rounded_inputs(ops, B, TA, TB, ragged):
     """Tensor-core path against the float64 oracle evaluated on the SAME bf16-rounded normalised tokens (isolates the
-    kernel arithmetic from input rounding; the argmax then agrees except at fp32-accumulation near-ties)."""
+    kernel arithmetic from input rounding; the argmax then agrees except at fp32-accumulation near-ties).
+    The forward has two implementations: the single sweep (csrc/filip_tc1.cu) when one modality has at most 512 tokens
+    -- A as the row side, or B when only TB fits (640 x 200) -- and one launch per side otherwise (600 x 520)."""
     from pclip import synth
     hA, hB, mA, mB, tau = synth.filip_tokens(B, TA, TB, cfg_id=300 + TA, ragged=ragged)
     if ragged:
