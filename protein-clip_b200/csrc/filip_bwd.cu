@@ -223,6 +223,113 @@ filip_invert_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, const i
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// inversion, one WARP per sample pair (Tx, Ty <= 512, groups of 4 rows): no block barrier anywhere, so 48 warps per SM
+// work on 48 pairs at once (the CTA-per-pair kernel above spends its time in __syncthreads: 0.56 ms per side at cfg 3).
+// Stable counting sort of the pair's <= 512 maximisers by target row:
+//   1. histogram of the target rows in a warp-private shared-memory array (the 16 coalesced index loads of the pair
+//      are in flight together and stay in registers for step 3)
+//   2. exclusive scan (lane = 16 consecutive rows) -> write cursors and the packed (first entry | count << 16) words
+//   3. batches of 32 columns in column order: rank among the lanes of the batch with the same row (ballots over the row's bits), entry
+//      to cursor + rank of a shared-memory image of the output; the first lane of each row advances the cursor
+//   4. the image goes out with coalesced 16-byte stores
+// The order -- (row, column) ascending -- is the one the CTA kernel produces, so the gradients stay bit-identical.
+// ---------------------------------------------------------------------------------------------------------
+namespace fb {
+constexpr int kWInvWarps = 8;
+constexpr int kWInvMax = 512;
+}  // namespace fb
+
+__global__ void __launch_bounds__(32 * fb::kWInvWarps, 4)
+filip_invert_warp_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, const int32_t* __restrict__ lenX,
+                         const int32_t* __restrict__ lenY, int Bx, int By, int Tx, int Ty, uint32_t* __restrict__ inv,
+                         uint32_t* __restrict__ grp2) {
+  using namespace fb;
+  __shared__ __align__(16) uint32_t cnt_s[kWInvWarps][kWInvMax];
+  __shared__ __align__(16) uint32_t out_s[kWInvWarps][kWInvMax];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t* cnt = cnt_s[warp];
+  uint32_t* img = out_s[warp];
+  const int G = filip_groups(Tx, 4);
+  const uint32_t lt = (1u << lane) - 1u;
+  for (int pair = blockIdx.x * kWInvWarps + warp; pair < Bx * By; pair += gridDim.x * kWInvWarps) {
+    const int x = pair / By, y = pair - x * By;
+    const int lx = min(lenX[x], Tx), ly = min(lenY[y], Ty);
+    uint32_t* go = grp2 + (int64_t)pair * G;
+    if (ly <= 0 || lx <= 0) {   // warp-uniform: no entries
+      for (int g = lane; g < G; g += 32) go[g] = 0u;
+      continue;
+    }
+    const int16_t* ay = argY + ((int64_t)y * Bx + x) * Ty;
+    uint32_t* out = inv + (int64_t)pair * Ty;
+    const int nb = (ly + 31) >> 5;
+    uint32_t tv[kWInvMax / 32];
+#pragma unroll
+    for (int b = 0; b < kWInvMax / 32; ++b) {
+      const int s = b * 32 + lane;
+      tv[b] = (b < nb && s < ly) ? (uint32_t)(uint16_t)__ldg(ay + s) : 0xffffu;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(cnt + lane * 16 + i * 4) = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+#pragma unroll
+    for (int b = 0; b < kWInvMax / 32; ++b)
+      if (tv[b] != 0xffffu) atomicAdd(&cnt[tv[b]], 1u);
+    __syncwarp();
+    // exclusive scan: lane owns rows 16 lane .. 16 lane + 15
+    uint32_t c[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint4 v = *reinterpret_cast<const uint4*>(cnt + lane * 16 + i * 4);
+      c[4 * i] = v.x, c[4 * i + 1] = v.y, c[4 * i + 2] = v.z, c[4 * i + 3] = v.w;
+    }
+    uint32_t tot = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tot += c[i];
+    uint32_t incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    uint32_t run = incl - tot;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t s0 = run, s1 = s0 + c[4 * i], s2 = s1 + c[4 * i + 1], s3 = s2 + c[4 * i + 2];
+      run = s3 + c[4 * i + 3];
+      *reinterpret_cast<uint4*>(cnt + lane * 16 + i * 4) = make_uint4(s0, s1, s2, s3);
+      if (lane * 4 + i < G) go[lane * 4 + i] = s0 | ((run - s0) << 16);
+    }
+    __syncwarp();
+    // placement, batch by batch in column order (stable)
+#pragma unroll
+    for (int b = 0; b < kWInvMax / 32; ++b) {
+      if (b < nb) {   // warp-uniform
+        const uint32_t t = tv[b];
+        const bool valid = t != 0xffffu;
+        uint32_t m = 0xffffffffu;   // lanes of the batch with the same row: 10 ballots (MATCH.ANY is far slower)
+#pragma unroll
+        for (int bit = 0; bit < 10; ++bit) {
+          const uint32_t bal = __ballot_sync(0xffffffffu, (t >> bit) & 1u);
+          m &= ((t >> bit) & 1u) ? bal : ~bal;
+        }
+        const uint32_t rank = __popc(m & lt);
+        const uint32_t base = valid ? cnt[t] : 0u;
+        if (valid) img[base + rank] = (t << 16) | (uint32_t)(b * 32 + lane);
+        __syncwarp();
+        if (valid && rank == 0) cnt[t] = base + __popc(m);
+        __syncwarp();
+      }
+    }
+    if ((Ty & 3) == 0) {
+      for (int i = lane * 4; i < ly; i += 128) *reinterpret_cast<uint4*>(out + i) = *reinterpret_cast<const uint4*>(img + i);
+    } else {
+      for (int i = lane; i < ly; i += 32) out[i] = img[i];
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // gradient: grid ceil(Bx * ceil(Tx / RPW) / WARPS), 32 * WARPS threads, (Bx + 1) ints of dynamic shared memory
 // ---------------------------------------------------------------------------------------------------------
 struct FilipGatherArgs {
@@ -456,9 +563,19 @@ int filip_gather_side(const __nv_bfloat16* Yr, const int32_t* lenX, const int32_
   filip_weights_kernel<<<(unsigned)ceil_div(Bx * By, 256), 256, 0, st>>>(lenX, lenY, (int)Bx, (int)By, (int)Tx, (int)Ty,
                                                                          tau, gX, gx0, gx1, gY, gy0, gy1, w2);
   PCLIP_CHECK_LAUNCH();
-  const int64_t inv_ctas = std::min<int64_t>(Bx * By, (int64_t)device_sm_count() * 4);
-  filip_invert_kernel<<<(unsigned)inv_ctas, fb::kInvThreads, 0, st>>>(argY, lenX, lenY, (int)Bx, (int)By, (int)Tx,
-                                                                      (int)Ty, rpw, inv, grp2);
+  static const bool cta_invert = [] {
+    const char* e = getenv("PCLIP_FILIP_INVERT");   // A/B switch: "cta" forces the CTA-per-pair inversion
+    return e && e[0] == 'c';
+  }();
+  if (!cta_invert && rpw == 4 && Tx <= fb::kWInvMax && Ty <= fb::kWInvMax) {
+    const int64_t blocks = std::min<int64_t>(ceil_div(Bx * By, (int64_t)fb::kWInvWarps), (int64_t)device_sm_count() * 4);
+    filip_invert_warp_kernel<<<(unsigned)blocks, 32 * fb::kWInvWarps, 0, st>>>(argY, lenX, lenY, (int)Bx, (int)By,
+                                                                               (int)Tx, (int)Ty, inv, grp2);
+  } else {
+    const int64_t inv_ctas = std::min<int64_t>(Bx * By, (int64_t)device_sm_count() * 4);
+    filip_invert_kernel<<<(unsigned)inv_ctas, fb::kInvThreads, 0, st>>>(argY, lenX, lenY, (int)Bx, (int)By, (int)Tx,
+                                                                        (int)Ty, rpw, inv, grp2);
+  }
   PCLIP_CHECK_LAUNCH();
   FilipGatherArgs a{(int)Bx, (int)By, (int)Tx, (int)Ty, lenX, w2, argX, inv, grp2, Yr, dX};
   PCLIP_REQUIRE(Bx <= 8192, PCLIP_ERR_UNSUPPORTED, "filip_bwd: at most 8192 samples per side (got %lld)", (long long)Bx);
