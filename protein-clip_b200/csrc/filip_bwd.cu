@@ -229,26 +229,31 @@ filip_invert_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, const i
 //   1. histogram of the target rows in a warp-private shared-memory array (the 16 coalesced index loads of the pair
 //      are in flight together and stay in registers for step 3)
 //   2. exclusive scan (lane = 16 consecutive rows) -> write cursors and the packed (first entry | count << 16) words
-//   3. batches of 32 columns in column order: rank among the lanes of the batch with the same row (ballots over the row's bits), entry
+//   3. batches of 32 columns in column order: rank among the lanes of the batch with the same row (each ORs its bit into the row's shared-memory word), entry
 //      to cursor + rank of a shared-memory image of the output; the first lane of each row advances the cursor
 //   4. the image goes out with coalesced 16-byte stores
 // The order -- (row, column) ascending -- is the one the CTA kernel produces, so the gradients stay bit-identical.
 // ---------------------------------------------------------------------------------------------------------
 namespace fb {
-constexpr int kWInvWarps = 8;
+constexpr int kWInvWarps = 4;
 constexpr int kWInvMax = 512;
 }  // namespace fb
 
-__global__ void __launch_bounds__(32 * fb::kWInvWarps, 4)
+__global__ void __launch_bounds__(32 * fb::kWInvWarps, 8)
 filip_invert_warp_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, const int32_t* __restrict__ lenX,
                          const int32_t* __restrict__ lenY, int Bx, int By, int Tx, int Ty, uint32_t* __restrict__ inv,
                          uint32_t* __restrict__ grp2) {
   using namespace fb;
   __shared__ __align__(16) uint32_t cnt_s[kWInvWarps][kWInvMax];
   __shared__ __align__(16) uint32_t out_s[kWInvWarps][kWInvMax];
+  __shared__ __align__(16) uint32_t bit_s[kWInvWarps][kWInvMax];   // per row: lanes of the current batch that target it
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint32_t* cnt = cnt_s[warp];
   uint32_t* img = out_s[warp];
+  uint32_t* bits = bit_s[warp];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(bits + lane * 16 + i * 4) = make_uint4(0u, 0u, 0u, 0u);
+  __syncwarp();
   const int G = filip_groups(Tx, 4);
   const uint32_t lt = (1u << lane) - 1u;
   for (int pair = blockIdx.x * kWInvWarps + warp; pair < Bx * By; pair += gridDim.x * kWInvWarps) {
@@ -306,17 +311,17 @@ filip_invert_warp_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, co
       if (b < nb) {   // warp-uniform
         const uint32_t t = tv[b];
         const bool valid = t != 0xffffu;
-        uint32_t m = 0xffffffffu;   // lanes of the batch with the same row: 10 ballots (MATCH.ANY is far slower)
-#pragma unroll
-        for (int bit = 0; bit < 10; ++bit) {
-          const uint32_t bal = __ballot_sync(0xffffffffu, (t >> bit) & 1u);
-          m &= ((t >> bit) & 1u) ? bal : ~bal;
-        }
+        if (valid) atomicOr(&bits[t], 1u << lane);   // lanes of the batch with the same row claim a bit of its word
+        __syncwarp();
+        const uint32_t m = valid ? bits[t] : 0u;
         const uint32_t rank = __popc(m & lt);
         const uint32_t base = valid ? cnt[t] : 0u;
         if (valid) img[base + rank] = (t << 16) | (uint32_t)(b * 32 + lane);
         __syncwarp();
-        if (valid && rank == 0) cnt[t] = base + __popc(m);
+        if (valid && rank == 0) {   // the row's first lane advances the cursor and clears the word
+          cnt[t] = base + __popc(m);
+          bits[t] = 0u;
+        }
         __syncwarp();
       }
     }
@@ -568,7 +573,7 @@ int filip_gather_side(const __nv_bfloat16* Yr, const int32_t* lenX, const int32_
     return e && e[0] == 'c';
   }();
   if (!cta_invert && rpw == 4 && Tx <= fb::kWInvMax && Ty <= fb::kWInvMax) {
-    const int64_t blocks = std::min<int64_t>(ceil_div(Bx * By, (int64_t)fb::kWInvWarps), (int64_t)device_sm_count() * 4);
+    const int64_t blocks = std::min<int64_t>(ceil_div(Bx * By, (int64_t)fb::kWInvWarps), (int64_t)device_sm_count() * 8);
     filip_invert_warp_kernel<<<(unsigned)blocks, 32 * fb::kWInvWarps, 0, st>>>(argY, lenX, lenY, (int)Bx, (int)By,
                                                                                (int)Tx, (int)Ty, inv, grp2);
   } else {
