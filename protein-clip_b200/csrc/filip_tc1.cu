@@ -483,14 +483,14 @@ int tc_filip_both_fwd(const __nv_bfloat16* X, const __nv_bfloat16* Y, const int3
   PCLIP_TRY(make_tmap_bf16_3d(&mx, X, (uint64_t)Bx, (uint64_t)Tx, f1::kDim, f1::kTile, 64));
   PCLIP_TRY(make_tmap_bf16_3d(&my, Y, (uint64_t)By, (uint64_t)Ty, f1::kDim, f1::kTile, 64));
   // y samples split over blockIdx.y so that the grid fills whole rounds of the SMs (one CTA per SM); a split costs the
-  // CTA's fixed part (TMEM allocation, barriers, up to 128 KB of X tiles: about a third of a full-length sample pair).
+  // CTA's fixed part (TMEM allocation, barriers, up to 128 KB of X tiles: about half a full-length sample pair).
   // cfg 3: 256 CTAs x 4 splits = 6.92 waves = 7 rounds of 64 pairs against 442.8 ideal.  The finest split within 1.5 %
   // of the best wins (ragged batches balance better).  PCLIP_FILIP_YSPLIT overrides.
   const int sms = std::max(device_sm_count(), 1);
   int ysplit = 1;
   {
     const int64_t cap = std::min<int64_t>(By, std::max<int64_t>(32, ceil_div(sms, Bx)));
-    auto cost = [&](int64_t ys) { return (double)ceil_div(Bx * ys, (int64_t)sms) * ((double)ceil_div(By, ys) + 0.3); };
+    auto cost = [&](int64_t ys) { return (double)ceil_div(Bx * ys, (int64_t)sms) * ((double)ceil_div(By, ys) + 0.6); };
     double best = 1e300;
     for (int64_t ys = 1; ys <= cap; ++ys) best = std::min(best, cost(ys));
     for (int64_t ys = 1; ys <= cap; ++ys)
