@@ -135,13 +135,16 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
 #ifndef PCLIP_MBAR_TIMEOUT_NS
 #define PCLIP_MBAR_TIMEOUT_NS 2000000000ull
 #endif
+#ifndef PCLIP_MBAR_HINT_NS
+#define PCLIP_MBAR_HINT_NS 4000u
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const uint64_t t0 = global_timer_ns();
   while (true) {
 #pragma unroll 1
     for (int i = 0; i < 64; ++i)
-      if (mbar_try_wait_hint(bar, parity, 4000u)) return;
+      if (mbar_try_wait_hint(bar, parity, PCLIP_MBAR_HINT_NS)) return;
     if (global_timer_ns() - t0 > PCLIP_MBAR_TIMEOUT_NS) {
       printf("pclip: mbarrier timeout block=(%d,%d) thread=%d bar=%u parity=%u\n", blockIdx.x, blockIdx.y,
              threadIdx.x, smem_u32(bar), parity);

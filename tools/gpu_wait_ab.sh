@@ -1,9 +1,11 @@
 #!/bin/bash
-# does the mbarrier wait loop (suspend hint) cost the CLIP / two-pass FILIP kernels anything?  (library built twice)
+# mbarrier wait loop: suspend-time hint A/B on the CLIP step and the FILIP forward (libraries built with -DPCLIP_MBAR_HINT_NS=...)
 mkdir -p gpurun_out
-for lib in hint nohint; do
-  cp build/ab/libpclip_$lib.so protein-clip_b200/pclip/libpclip.so
-  echo "== $lib" | tee -a gpurun_out/wait_ab.log
+cp protein-clip_b200/pclip/libpclip.so /tmp/libpclip_orig.so
+for h in 200 4000 20000 200 4000 20000; do
+  cp tools/bin/ab/libpclip_h$h.so protein-clip_b200/pclip/libpclip.so
+  echo "== hint $h ns" | tee -a gpurun_out/wait_ab.log
   timeout 200 python bench.py --steps 10 --warmup 3 --no-extras 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('clip ms', d['ms_per_step'], d['roofline']['kernel_ms'], d['roofline']['other_kernels_ms'])" | tee -a gpurun_out/wait_ab.log
-  for fwd in 0 2; do PCLIP_FILIP_FWD=$fwd timeout 120 python tools/gpu_filip_split.py full 2>&1 | grep "filip_fwd" | tee -a gpurun_out/wait_ab.log; done
+  timeout 120 python tools/gpu_filip_split.py full 2>&1 | grep "filip_fwd" | tee -a gpurun_out/wait_ab.log
 done
+cp /tmp/libpclip_orig.so protein-clip_b200/pclip/libpclip.so
