@@ -5,18 +5,22 @@
 // tcgen05.ld.16x256b instead of .32x32b: a thread then holds a 4-row x 8-column patch of each 32 x 32 chunk (rows
 // g + 8j, columns 8k + 2c + e of the warp's 32 TMEM lanes; g = lane / 4, c = lane % 4 -- the mma.m16n8 accumulator
 // layout), so BOTH directions start with an in-thread reduction:
-//   row direction     8 keys of a row -> 1 in-thread (FMNMX3 tree), kept as a running maximum per (row, lane) over the
-//                     column sample's tiles; the 4 lanes that share a row are combined once per sample pair
-//   column direction  4 keys of a column -> 1 in-thread, then a transposing butterfly over the 8 lanes that share the
-//                     column set (7 SHFL + 7 FMNMX + 14 SEL per 32 x 32 chunk) leaves one column winner per lane;
-//                     the winners of the (row tile, lane quarter) warps meet in shared memory, where a finaliser warp
-//                     picks the maximiser over all rows of the sample and writes argY / the masked-mean partial sum
+//   row direction     8 keys of a row -> 1 in-thread (FMNMX3 tree); the chunk winners of a tile are merged by plain
+//                     maxima (the chunk id rides in the key's j bits) and compared with the running maximum per
+//                     (row, lane) once per tile; the 4 lanes that share a row are combined once per sample pair
+//   column direction  4 keys of a column -> 1 in-thread; the 8 lane groups g that share a column set exchange their
+//                     candidates through a warp-private 1 KB shared-memory patch (conflict-free [column slot][g]
+//                     layout), which leaves one column winner per lane; the winners of the 16 (row tile, lane quarter)
+//                     warps meet in shared memory, where a finaliser warp picks the maximiser over all rows of the
+//                     sample (FMNMX3 tree over slot-tagged keys) and writes argY / the masked-mean partial sum
 // One key serves both directions: the score with its 5 low mantissa bits replaced by 31 - (8j + 2k + e) (ONE LOP3);
-// within a row j is constant, within a column (k, e) is.  Before the butterfly the 3 column bits are replaced by
+// within a row j is constant, within a column (k, e) is.  Before the exchange the 3 column bits are replaced by
 // 7 - g, so the 5 bits of a column winner are 31 - (row within the warp's 32 lanes).  Tie rule as in filip_tc.cu:
 // scores equal to 2^-18 relative are tied and the lowest index wins.
 // The CTA owns ALL rows of one row sample (up to 4 row tiles stationary in shared memory; the 4 TMEM accumulators are
-// a ring over the (column tile, row tile) sequence), so the column maxima are complete inside the CTA.
+// a ring over the (column tile, row tile) sequence), so the column maxima are complete inside the CTA.  Warps: TMA
+// producer, MMA issuer, 16 epilogue warps (row tile h x lane quarter q), column finaliser.  The kernel is bound by the
+// ALU pipe (LOP3 / FMNMX: 81 % active), then by the power-limited tensor rate; DESIGN.md section 4 has the measured history.
 #include <cuda_bf16.h>
 #include <float.h>
 
@@ -24,9 +28,6 @@
 #include "ptx.cuh"
 
 namespace pclip {
-
-int filip_finalize(const float* part, int np, const int32_t* lenX, int Bx, int By, int Tx, const float* tau, float* out,
-                   int64_t so0, int64_t so1, cudaStream_t st);
 
 namespace f1 {
 constexpr int kTile = 128;
