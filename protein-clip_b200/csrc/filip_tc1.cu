@@ -211,7 +211,7 @@ tc_filip_both_kernel(const __grid_constant__ CUtensorMap tx, const __grid_consta
   using namespace f1;
   const int bx = blockIdx.x;
   const int y0 = blockIdx.y * args.y_per_split, y1 = min(y0 + args.y_per_split, args.By);
-  const int lx = min(args.lenX[bx], args.Tx);
+  const int lx = max(min(args.lenX[bx], args.Tx), 0);
   const int nh = (lx + kTile - 1) / kTile;   // row tiles that hold at least one valid token (0..4)
 
   extern __shared__ uint8_t smem_raw[];
