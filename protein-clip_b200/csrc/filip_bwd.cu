@@ -223,7 +223,7 @@ filip_invert_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, const i
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// inversion, one WARP per sample pair (Tx, Ty <= 512, groups of 4 rows): no block barrier anywhere, so 48 warps per SM
+// inversion, one WARP per sample pair (Tx, Ty <= 512, groups of 4 or 8 rows): no block barrier anywhere, so 48 warps per SM
 // work on 48 pairs at once (the CTA-per-pair kernel above spends its time in __syncthreads: 0.56 ms per side at cfg 3).
 // Stable counting sort of the pair's <= 512 maximisers by target row:
 //   1. histogram of the target rows in a warp-private shared-memory array (the 16 coalesced index loads of the pair
@@ -241,8 +241,8 @@ constexpr int kWInvMax = 512;
 
 __global__ void __launch_bounds__(32 * fb::kWInvWarps, 8)
 filip_invert_warp_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, const int32_t* __restrict__ lenX,
-                         const int32_t* __restrict__ lenY, int Bx, int By, int Tx, int Ty, uint32_t* __restrict__ inv,
-                         uint32_t* __restrict__ grp2) {
+                         const int32_t* __restrict__ lenY, int Bx, int By, int Tx, int Ty, int gs /* 4 or 8 */,
+                         uint32_t* __restrict__ inv, uint32_t* __restrict__ grp2) {
   using namespace fb;
   __shared__ __align__(16) uint32_t cnt_s[kWInvWarps][kWInvMax];
   __shared__ __align__(16) uint32_t out_s[kWInvWarps][kWInvMax];
@@ -254,7 +254,7 @@ filip_invert_warp_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, co
 #pragma unroll
   for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(bits + lane * 16 + i * 4) = make_uint4(0u, 0u, 0u, 0u);
   __syncwarp();
-  const int G = filip_groups(Tx, 4);
+  const int G = filip_groups(Tx, gs);
   const uint32_t lt = (1u << lane) - 1u;
   for (int pair = blockIdx.x * kWInvWarps + warp; pair < Bx * By; pair += gridDim.x * kWInvWarps) {
     const int x = pair / By, y = pair - x * By;
@@ -296,13 +296,19 @@ filip_invert_warp_kernel(const int16_t* __restrict__ argY /* [By][Bx][Ty] */, co
       const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
       if (lane >= o) incl += v;
     }
-    uint32_t run = incl - tot;
+    uint32_t run = incl - tot, first8 = 0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const uint32_t s0 = run, s1 = s0 + c[4 * i], s2 = s1 + c[4 * i + 1], s3 = s2 + c[4 * i + 2];
       run = s3 + c[4 * i + 3];
       *reinterpret_cast<uint4*>(cnt + lane * 16 + i * 4) = make_uint4(s0, s1, s2, s3);
-      if (lane * 4 + i < G) go[lane * 4 + i] = s0 | ((run - s0) << 16);
+      if (gs == 4) {
+        if (lane * 4 + i < G) go[lane * 4 + i] = s0 | ((run - s0) << 16);
+      } else if ((i & 1) == 0) {
+        first8 = s0;
+      } else if (lane * 2 + (i >> 1) < G) {
+        go[lane * 2 + (i >> 1)] = first8 | ((run - first8) << 16);
+      }
     }
     __syncwarp();
     // placement, batch by batch in column order (stable)
@@ -572,10 +578,10 @@ int filip_gather_side(const __nv_bfloat16* Yr, const int32_t* lenX, const int32_
     const char* e = getenv("PCLIP_FILIP_INVERT");   // A/B switch: "cta" forces the CTA-per-pair inversion
     return e && e[0] == 'c';
   }();
-  if (!cta_invert && rpw == 4 && Tx <= fb::kWInvMax && Ty <= fb::kWInvMax) {
+  if (!cta_invert && Tx <= fb::kWInvMax && Ty <= fb::kWInvMax) {
     const int64_t blocks = std::min<int64_t>(ceil_div(Bx * By, (int64_t)fb::kWInvWarps), (int64_t)device_sm_count() * 8);
     filip_invert_warp_kernel<<<(unsigned)blocks, 32 * fb::kWInvWarps, 0, st>>>(argY, lenX, lenY, (int)Bx, (int)By,
-                                                                               (int)Tx, (int)Ty, inv, grp2);
+                                                                               (int)Tx, (int)Ty, rpw, inv, grp2);
   } else {
     const int64_t inv_ctas = std::min<int64_t>(Bx * By, (int64_t)device_sm_count() * 4);
     filip_invert_kernel<<<(unsigned)inv_ctas, fb::kInvThreads, 0, st>>>(argY, lenX, lenY, (int)Bx, (int)By, (int)Tx,
