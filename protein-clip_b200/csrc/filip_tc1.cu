@@ -68,7 +68,8 @@ __device__ __forceinline__ void tmem_ld_16x256b_x4(uint32_t taddr, uint32_t* r) 
       : "memory");
 }
 
-// a 32-row x 32-column chunk of the warp's lane quarter: r[16 (j >> 1) + 4k + 2 (j & 1) + e] = (row g + 8j, column 8k + 2c + e)
+// a 32-row x 32-column chunk of the warp's lane quarter:
+//   r[16 (j >> 1) + 4k + 2 (j & 1) + e] = (row g + 8j, column 8k + 2c + e)
 __device__ __forceinline__ void load_chunk(uint32_t taddr, uint32_t (&r)[32]) {
   tmem_ld_16x256b_x4(taddr, &r[0]);
   tmem_ld_16x256b_x4(taddr + (16u << 16), &r[16]);
@@ -121,8 +122,8 @@ struct Patch {         // this lane's addresses in its warp's transposition patc
   uint32_t gcode;      // 7 - g
 };
 
-// One 32 x 32 chunk (chunk cc of its tile).  nv = valid columns of the chunk (>= 1; < 32 only in a column sample's last tile), rowmask: bit j
-// set = row g + 8j is a pad row (excluded from the column maxima).  Returns the winner of column
+// One 32 x 32 chunk (chunk cc of its tile).  nv = valid columns of the chunk (>= 1; < 32 only in a column sample's
+// last tile), rowmask: bit j set = row g + 8j is a pad row (excluded from the column maxima).  Returns the winner of column
 // 8 (lane >> 3) + 2 (lane & 3) + ((lane >> 2) & 1) of the chunk, low 5 bits = 31 - (winning row within the warp's 32).
 __device__ __forceinline__ uint32_t chunk_both(uint32_t (&r)[32], const int cc, const int nv, const uint32_t rowmask,
                                                const int lane, float (&rowwin)[4], const Patch& pa) {
@@ -154,7 +155,7 @@ __device__ __forceinline__ uint32_t chunk_both(uint32_t (&r)[32], const int cc, 
     asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(v) : "r"(m), "r"(cmask), "r"(ccode));
     rowwin[j] = cc == 0 ? __uint_as_float(v) : fmaxf(rowwin[j], __uint_as_float(v));
   }
-  // column direction: pad rows out, 4 rows -> 1 in-thread, row-in-warp code, butterfly over g
+  // column direction: pad rows out first
   if (rowmask) {
 #pragma unroll
     for (int j = 0; j < 4; ++j)
